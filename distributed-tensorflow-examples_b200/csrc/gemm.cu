@@ -1,0 +1,334 @@
+// Dense GEMM with fused epilogue on the 5th-generation tensor cores.
+//
+//   acc[m,n] = alpha * sum_k A[m,k] * B[n,k]      A:[M,K] bf16, B:[N,K] bf16 (both K-major)
+//
+// One CTA per 128 x BN output tile, 6 warps:
+//   warp 0      TMA producer   (cp.async.bulk.tensor, 128B swizzle, kStages-deep ring)
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (fp32 accum in TMEM)
+//   warps 2..5  epilogue: tcgen05.ld -> bias / activation / activation-derivative ->
+//               bf16 row-major, bf16 transposed, fp32, and column-sum outputs
+//
+// Serves every dense call site of the three reference models (forward, dgrad, wgrad):
+// encoder:69-84,137  gan:77-92,158-159  lstm:53,97 — see include/psb200.h.
+#include "../../include/psb200.h"
+#include "host_common.h"
+#include "ptx.cuh"
+
+namespace psb {
+
+constexpr int kBM = 128;          // tile rows   (UMMA M)
+constexpr int kBK = 64;           // K per stage (one 128-byte swizzle atom of bf16)
+constexpr int kUmmaK = 16;
+constexpr int kGemmThreads = 192;
+constexpr int kMaxSmem = 200 * 1024;
+
+struct EpiArgs {
+    float alpha;
+    int act;
+    int dact;
+    const float* bias;
+    const __nv_bfloat16* yprev;
+    int ld_yprev;
+    __nv_bfloat16* out;
+    int ld_out;
+    __nv_bfloat16* out_t;
+    int ld_out_t;
+    float* out_f32;
+    int ld_f32;
+    float* colsum;
+};
+
+__host__ __device__ constexpr int stage_bytes(int bn) { return kBM * 128 + bn * 128; }
+
+__host__ inline int pick_stages(int bn, int num_kb) {
+    int s = (kMaxSmem - 1024) / stage_bytes(bn);
+    if (s > 8) s = 8;
+    if (s > num_kb) s = num_kb;
+    if (s < 1) s = 1;
+    return s;
+}
+
+// After the call, lane l of the warp holds (in the return value) the sum over all 32 lanes of
+// v[l].  31 shuffles instead of 32 x 5.
+__device__ __forceinline__ float warp_transpose_reduce(float (&v)[32], uint32_t lane) {
+#pragma unroll
+    for (int off = 16, n = 32; off >= 1; off >>= 1, n >>= 1) {
+        const bool upper = (lane & off) != 0;
+#pragma unroll
+        for (int i = 0; i < n / 2; ++i) {
+            float send = upper ? v[i] : v[i + n / 2];
+            float keep = upper ? v[i + n / 2] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+    }
+    return v[0];
+}
+
+template <int BN>
+__device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, float (&v)[32], int row, int n_base,
+                                               int M, int N, uint32_t lane) {
+    const bool row_ok = row < M;
+    // ---- bias + activation
+#pragma unroll
+    for (int j = 0; j < 32; ++j) {
+        const int n = n_base + j;
+        float x = v[j] * e.alpha;
+        if (e.bias != nullptr && n < N) x += __ldg(e.bias + n);
+        if (e.act == 1) x = fast_sigmoid(x);
+        else if (e.act == 2) x = fmaxf(x, 0.0f);
+        v[j] = x;
+    }
+    // ---- multiply by the derivative of the activation that produced yprev
+    if (e.yprev != nullptr && row_ok) {
+        const __nv_bfloat16* yp = e.yprev + static_cast<size_t>(row) * e.ld_yprev + n_base;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (n_base + 8 * g < e.ld_yprev) {
+                uint4 raw = *reinterpret_cast<const uint4*>(yp + 8 * g);
+                const __nv_bfloat16* y8 = reinterpret_cast<const __nv_bfloat16*>(&raw);
+#pragma unroll
+                for (int t = 0; t < 8; ++t) {
+                    float y = __bfloat162float(y8[t]);
+                    float d = (e.dact == 1) ? y * (1.0f - y) : ((y > 0.0f) ? 1.0f : 0.0f);
+                    v[8 * g + t] *= d;
+                }
+            }
+        }
+    }
+    // ---- zero everything outside the logical matrix (pad columns / pad rows)
+#pragma unroll
+    for (int j = 0; j < 32; ++j)
+        if (!row_ok || n_base + j >= N) v[j] = 0.0f;
+
+    // ---- bf16 row-major
+    if (e.out != nullptr && row_ok) {
+        __nv_bfloat16* o = e.out + static_cast<size_t>(row) * e.ld_out + n_base;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            if (n_base + 8 * g < e.ld_out && n_base + 8 * g < ((N + 7) & ~7)) {
+                uint4 pk;
+                __nv_bfloat162* p2 = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    p2[t] = __floats2bfloat162_rn(v[8 * g + 2 * t], v[8 * g + 2 * t + 1]);
+                *reinterpret_cast<uint4*>(o + 8 * g) = pk;
+            }
+        }
+    }
+    // ---- bf16 transposed: for a fixed column the 32 lanes write 32 consecutive rows
+    if (e.out_t != nullptr && row_ok) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+            const int n = n_base + j;
+            if (n < N) e.out_t[static_cast<size_t>(n) * e.ld_out_t + row] = __float2bfloat16_rn(v[j]);
+        }
+    }
+    // ---- fp32 row-major
+    if (e.out_f32 != nullptr && row_ok) {
+        float* o = e.out_f32 + static_cast<size_t>(row) * e.ld_f32 + n_base;
+        if ((N & 3) == 0 && (e.ld_f32 & 3) == 0) {
+#pragma unroll
+            for (int g = 0; g < 8; ++g)
+                if (n_base + 4 * g < N)
+                    *reinterpret_cast<float4*>(o + 4 * g) =
+                        make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (n_base + j < N) o[j] = v[j];
+        }
+    }
+    // ---- column sums (bias gradient)
+    if (e.colsum != nullptr) {
+        float s = warp_transpose_reduce(v, lane);
+        const int n = n_base + static_cast<int>(lane);
+        if (n < N) atomicAdd(e.colsum + n, s);
+    }
+}
+
+template <int BN>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 int M, int N, int K, int stages, EpiArgs epi) {
+    extern __shared__ uint8_t smem_raw[];
+    // 128B-swizzled tiles need 1024-byte alignment
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int kStage = stage_bytes(BN);
+    constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;
+
+    __shared__ __align__(8) uint64_t full_bar[8];
+    __shared__ __align__(8) uint64_t empty_bar[8];
+    __shared__ __align__(8) uint64_t tmem_full_bar;
+    __shared__ uint32_t tmem_base_slot;
+
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t lane = lane_id();
+    const int m0 = blockIdx.y * kBM;
+    const int n0 = blockIdx.x * BN;
+    const int num_kb = (K + kBK - 1) / kBK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tma_a);
+        tma_prefetch_desc(&tma_b);
+        for (int s = 0; s < stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(&tmem_full_bar, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc<kTmemCols>(&tmem_base_slot);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = tmem_base_slot;
+
+    if (warp == 0) {
+        // ===================== TMA producer =====================
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                uint8_t* a_dst = smem + s * kStage;
+                uint8_t* b_dst = a_dst + kBM * 128;
+                mbar_expect_tx(&full_bar[s], kStage);
+                tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
+                tma_load_2d(b_dst, &tma_b, &full_bar[s], kb * kBK, n0);
+                if (++s == stages) { s = 0; ph ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================== MMA issuer =====================
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN);
+            int s = 0;
+            uint32_t ph = 0;
+            for (int kb = 0; kb < num_kb; ++kb) {
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after_sync();
+                const uint32_t a_addr = smem_u32(smem + s * kStage);
+                const uint32_t b_addr = a_addr + kBM * 128;
+                const uint64_t da = umma_desc_k128(a_addr);
+                const uint64_t db = umma_desc_k128(b_addr);
+#pragma unroll
+                for (int k = 0; k < kBK / kUmmaK; ++k) {
+                    // +32 bytes per K=16 step inside the swizzle atom (>>4 => +2)
+                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);   // frees the smem slot when these MMAs retire
+                if (++s == stages) { s = 0; ph ^= 1; }
+            }
+            umma_commit(&tmem_full_bar);      // accumulator complete
+        }
+    } else {
+        // ===================== epilogue =====================
+        mbar_wait(&tmem_full_bar, 0);
+        tc_fence_after_sync();
+        const uint32_t quad = warp & 3;       // TMEM lane quadrant this warp may read
+        const int row = m0 + static_cast<int>(quad * 32 + lane);
+        const uint32_t t_row = tmem_base + ((quad * 32u) << 16);
+        if constexpr (BN >= 32) {
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                if (n0 + c >= ((N + 7) & ~7)) break;   // warp-uniform
+                uint32_t r[32];
+                tmem_ld_32x32(t_row + c, r);
+                tmem_ld_wait();
+                float v[32];
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                epilogue_chunk<BN>(epi, v, row, n0 + c, M, N, lane);
+            }
+        } else {
+            uint32_t r[16];
+            tmem_ld_32x16(t_row, r);
+            tmem_ld_wait();
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+#pragma unroll
+            for (int j = 16; j < 32; ++j) v[j] = 0.0f;
+            // columns 16..31 are beyond this tile: treat them as outside the matrix
+            epilogue_chunk<BN>(epi, v, row, n0, M, (N < n0 + 16) ? N : n0 + 16, lane);
+        }
+        tc_fence_before_sync();
+    }
+
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after_sync();
+        tmem_dealloc<kTmemCols>(tmem_base);
+    }
+}
+
+template <int BN>
+static int launch_gemm(const CUtensorMap* ta, const CUtensorMap* tb, int M, int N, int K,
+                       const EpiArgs& e, cudaStream_t st) {
+    const int num_kb = (K + kBK - 1) / kBK;
+    const int stages = pick_stages(BN, num_kb);
+    const size_t smem = static_cast<size_t>(stages) * stage_bytes(BN) + 1024;
+    static bool attr_set = false;  // per instantiation
+    if (!attr_set) {
+        PSB_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<BN>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+        attr_set = true;
+    }
+    dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM);
+    gemm_bf16_kernel<BN><<<grid, kGemmThreads, smem, st>>>(*ta, *tb, M, N, K, stages, e);
+    return after_launch("gemm_bf16");
+}
+
+}  // namespace psb
+
+extern "C" int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                             const psb_epilogue_t* epi, int block_n, void* stream) {
+    using namespace psb;
+    if (!A || !B || !epi) return fail(PSB_ERR_ARG, "psb_gemm_bf16: null pointer argument");
+    if (M <= 0 || N <= 0 || K <= 0) return fail(PSB_ERR_ARG, "psb_gemm_bf16: M, N, K must be positive");
+    if (lda < K || ldb < K) return fail(PSB_ERR_ARG, "psb_gemm_bf16: leading dimension smaller than K");
+    if (epi->yprev && (epi->ld_yprev % 8 || epi->dact < 1 || epi->dact > 2))
+        return fail(PSB_ERR_ARG, "psb_gemm_bf16: yprev needs ld%%8==0 and dact in {1,2}");
+    if (epi->out && epi->ld_out % 8) return fail(PSB_ERR_ARG, "psb_gemm_bf16: ld_out must be a multiple of 8");
+    if (epi->out && epi->ld_out < ((N + 7) & ~7))
+        return fail(PSB_ERR_ARG, "psb_gemm_bf16: ld_out must cover N rounded up to 8");
+
+    int bn = block_n;
+    if (bn == 0) {
+        const int mt = (M + kBM - 1) / kBM;
+        bn = (N <= 16) ? 16 : 32;
+        const int cands[4] = {256, 128, 64, 32};
+        for (int c : cands) {
+            if (c <= 16) break;
+            if (mt * ((N + c - 1) / c) >= 148 && N >= c) { bn = c; break; }
+        }
+    }
+    const CUtensorMap* ta = tensor_map_bf16_2d(A, M, K, lda, kBM);
+    if (!ta) return PSB_ERR_DRIVER;
+    const CUtensorMap* tb = tensor_map_bf16_2d(B, N, K, ldb, bn);
+    if (!tb) return PSB_ERR_DRIVER;
+
+    EpiArgs e;
+    e.alpha = epi->alpha;
+    e.act = epi->act;
+    e.dact = epi->dact;
+    e.bias = epi->bias;
+    e.yprev = static_cast<const __nv_bfloat16*>(epi->yprev);
+    e.ld_yprev = epi->ld_yprev;
+    e.out = static_cast<__nv_bfloat16*>(epi->out);
+    e.ld_out = epi->ld_out;
+    e.out_t = static_cast<__nv_bfloat16*>(epi->out_t);
+    e.ld_out_t = epi->ld_out_t;
+    e.out_f32 = epi->out_f32;
+    e.ld_f32 = epi->ld_f32;
+    e.colsum = epi->colsum;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    switch (bn) {
+        case 16: return launch_gemm<16>(ta, tb, M, N, K, e, st);
+        case 32: return launch_gemm<32>(ta, tb, M, N, K, e, st);
+        case 64: return launch_gemm<64>(ta, tb, M, N, K, e, st);
+        case 128: return launch_gemm<128>(ta, tb, M, N, K, e, st);
+        case 256: return launch_gemm<256>(ta, tb, M, N, K, e, st);
+        default: return fail(PSB_ERR_ARG, "psb_gemm_bf16: block_n must be 0, 16, 32, 64, 128 or 256");
+    }
+}

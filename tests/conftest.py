@@ -1,0 +1,34 @@
+"""pytest configuration: the ``gpu`` marker and repo-root imports.
+
+``pytest -m "not gpu"`` runs everywhere (CPU, gloo, loopback TCP);
+``pytest -m gpu`` needs a B200 and the built kernel library.
+"""
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (B200) and the built sm_100a library")
+    config.addinivalue_line("markers", "multigpu: needs at least two CUDA devices")
+
+
+def pytest_collection_modifyitems(config, items):
+    try:
+        import torch
+        have = torch.cuda.is_available()
+        ngpu = torch.cuda.device_count() if have else 0
+    except Exception:  # pragma: no cover
+        have, ngpu = False, 0
+    skip_gpu = pytest.mark.skip(reason="no CUDA device")
+    skip_multi = pytest.mark.skip(reason="needs >= 2 CUDA devices")
+    for item in items:
+        if "gpu" in item.keywords and not have:
+            item.add_marker(skip_gpu)
+        if "multigpu" in item.keywords and ngpu < 2:
+            item.add_marker(skip_multi)

@@ -1,0 +1,79 @@
+"""T2: tcgen05 GEMM + epilogue vs an fp32 torch oracle (reference shapes incl. the awkward
+K=100/156, N=1/10 of gan:57,126 and lstm:31-34)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _mats(M, N, K, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    a = torch.randn(M, K, generator=g) * 0.5
+    b = torch.randn(N, K, generator=g) * 0.5
+    return a.cuda(), b.cuda()
+
+
+@pytest.mark.parametrize("M,N,K,bn", [
+    (128, 32, 64, 32), (128, 64, 128, 64), (256, 256, 784, 0), (256, 128, 256, 32),
+    (128, 784, 256, 64), (128, 1, 256, 0), (128, 10, 128, 16), (128, 256, 100, 0),
+    (784, 256, 256, 128), (100, 256, 128, 0), (300, 520, 456, 256), (256, 784, 256, 256),
+    (1024, 2048, 1024, 0),
+])
+def test_gemm_plain(M, N, K, bn):
+    from psb200.ops import cuda as K_
+    a, b = _mats(M, N, K)
+    A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
+    out = K_.BMat(M, N)
+    out_t = K_.BMat(N, M)
+    out_f = torch.full((M, N), float("nan"), device="cuda")
+    K_.gemm(A, B, out=out, out_t=out_t, out_f32=out_f, block_n=bn)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float().t()
+    tol = 2e-2 * max(1.0, ref.abs().max().item())
+    assert torch.allclose(out_f, ref, atol=1e-3 * max(1.0, ref.abs().max().item()), rtol=1e-4)
+    assert (out.float() - ref).abs().max().item() < tol
+    assert (out_t.float().t() - ref).abs().max().item() < tol
+    # pad columns stay zero
+    if out.ld > N:
+        assert out.t[:, N:].abs().max().item() == 0
+
+
+@pytest.mark.parametrize("act", [0, 1, 2])
+def test_gemm_bias_act(act):
+    from psb200.ops import cuda as K_
+    M, N, K = 256, 200, 784
+    a, b = _mats(M, N, K, 1)
+    a *= 0.2
+    bias = torch.randn(N, device="cuda")
+    A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
+    out = K_.BMat(M, N)
+    K_.gemm(A, B, bias=bias, act=act, out=out)
+    torch.cuda.synchronize()
+    ref = A.float() @ B.float().t() + bias
+    if act == 1:
+        ref = torch.sigmoid(ref)
+    elif act == 2:
+        ref = torch.relu(ref)
+    assert (out.float() - ref).abs().max().item() < 2e-2 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.parametrize("dact", [1, 2])
+def test_gemm_dact_colsum(dact):
+    from psb200.ops import cuda as K_
+    M, N, K = 256, 128, 256
+    a, b = _mats(M, N, K, 2)
+    y = torch.rand(M, N, device="cuda") if dact == 1 else torch.randn(M, N, device="cuda").relu()
+    Y = K_.BMat.from_tensor(y)
+    A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
+    out = K_.BMat(M, N)
+    out_t = K_.BMat(N, M)
+    colsum = torch.zeros(N, device="cuda")
+    K_.gemm(A, B, alpha=0.5, yprev=Y, dact=dact, out=out, out_t=out_t, colsum=colsum)
+    torch.cuda.synchronize()
+    yf = Y.float()
+    d = yf * (1 - yf) if dact == 1 else (yf > 0).float()
+    ref = 0.5 * (A.float() @ B.float().t()) * d
+    scale = max(1.0, ref.abs().max().item())
+    assert (out.float() - ref).abs().max().item() < 2e-2 * scale
+    assert (out_t.float().t() - ref).abs().max().item() < 2e-2 * scale
+    assert (colsum - ref.sum(0)).abs().max().item() < 1e-2 * max(1.0, ref.sum(0).abs().max().item())
