@@ -91,3 +91,101 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
         raise ValueError("gemm: out_t must be [%d,%d]" % (N, M))
     check(_lib.lib().psb_gemm_bf16(a.ptr, a.ld, b.ptr, b.ld, M, N, K, e, block_n,
                                    current_stream_ptr()), "psb_gemm_bf16")
+
+
+# --------------------------------------------------------------------------- LSTM
+from ctypes import c_float, c_int, c_void_p  # noqa: E402
+
+_lib.register_signature("psb_lstm_fwd", [c_void_p, c_void_p, c_int, c_void_p, c_float, c_int, c_int,
+                                         c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p,
+                                         c_void_p, c_void_p, c_int, c_void_p])
+_lib.register_signature("psb_lstm_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int,
+                                         c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p])
+_lib.register_signature("psb_cast_transpose", [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                                               c_void_p, c_int, c_void_p])
+_lib.register_signature("psb_mse_sigmoid_grad", [c_void_p, c_int, c_void_p, c_int, c_int, c_int,
+                                                 c_void_p, c_void_p, c_int, c_void_p, c_int,
+                                                 c_void_p, c_void_p])
+_lib.register_signature("psb_gan_loss_grad", [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int,
+                                              c_void_p, c_void_p, c_int, c_void_p, c_void_p])
+_lib.register_signature("psb_softmax_xent_grad", [c_void_p, c_int, c_void_p, c_int, c_int, c_int,
+                                                  c_void_p, c_void_p, c_int, c_void_p, c_int,
+                                                  c_void_p, c_void_p, c_void_p])
+
+
+class LstmSaved:
+    """Buffers the forward kernel fills for BPTT (preallocated once per plan)."""
+
+    def __init__(self, B: int, T: int, I: int, H: int, device="cuda"):
+        self.B, self.T, self.I, self.H = B, T, I, H
+        self.gates = torch.zeros(T, 4, B, H, dtype=torch.bfloat16, device=device)
+        self.c_all = torch.zeros(T, B, H, dtype=torch.float32, device=device)
+        self.xh_t = BMat(I + H, T * B, device)       # [I+H, T*B]
+        self.dg_t = BMat(4 * H, T * B, device)       # [4H, T*B]
+
+
+def lstm_fwd(x: torch.Tensor, wt: BMat, bias: torch.Tensor, forget_bias: float,
+             h_last: Optional[BMat] = None, h_last_t: Optional[BMat] = None,
+             saved: Optional[LstmSaved] = None, wt_ptr: Optional[int] = None) -> None:
+    """``x`` fp32 [B,T,I]; ``wt`` = cell kernel transposed, bf16 [4H, I+H].  ``wt_ptr`` overrides
+    the weight address (a peer GPU's copy) while ``wt`` still supplies the geometry."""
+    B, T, I = x.shape
+    H = wt.rows // 4
+    check(_lib.lib().psb_lstm_fwd(
+        x.data_ptr(), wt_ptr if wt_ptr is not None else wt.ptr, wt.ld, bias.data_ptr(),
+        float(forget_bias), B, T, I, H,
+        _ptr(h_last), h_last.ld if h_last is not None else 0,
+        _ptr(h_last_t), h_last_t.ld if h_last_t is not None else 0,
+        saved.gates.data_ptr() if saved else None, saved.c_all.data_ptr() if saved else None,
+        saved.xh_t.ptr if saved else None, saved.xh_t.ld if saved else 0,
+        current_stream_ptr()), "psb_lstm_fwd")
+
+
+def lstm_bwd(w: BMat, dh_last: torch.Tensor, saved: LstmSaved, dbias: torch.Tensor,
+             w_ptr: Optional[int] = None) -> None:
+    """``w`` = cell kernel natural layout bf16 [I+H, 4H]; ``dh_last`` fp32 [B,H]; fills
+    ``saved.dg_t`` and atomically accumulates ``dbias`` fp32 [4H]."""
+    check(_lib.lib().psb_lstm_bwd(
+        w_ptr if w_ptr is not None else w.ptr, w.ld, dh_last.data_ptr(), dh_last.stride(0),
+        saved.gates.data_ptr(), saved.c_all.data_ptr(), saved.B, saved.T, saved.I, saved.H,
+        saved.dg_t.ptr, saved.dg_t.ld, dbias.data_ptr(), current_stream_ptr()), "psb_lstm_bwd")
+
+
+# --------------------------------------------------------------------------- cast / losses
+def cast_transpose(x: torch.Tensor, out: Optional[BMat] = None, out_t: Optional[BMat] = None,
+                   out_ptr: Optional[int] = None, out_t_ptr: Optional[int] = None) -> None:
+    """fp32 [M,N] -> bf16 ``out`` [M,N] and/or ``out_t`` [N,M].  ``out_ptr``/``out_t_ptr``
+    redirect the write into a sub-block of a larger matrix (same leading dimensions)."""
+    M, N = x.shape
+    check(_lib.lib().psb_cast_transpose(
+        x.data_ptr(), x.stride(0), M, N,
+        out_ptr if out_ptr is not None else _ptr(out), out.ld if out is not None else 0,
+        out_t_ptr if out_t_ptr is not None else _ptr(out_t), out_t.ld if out_t is not None else 0,
+        current_stream_ptr()), "psb_cast_transpose")
+
+
+def mse_sigmoid_grad(y: torch.Tensor, x: torch.Tensor, loss: torch.Tensor, dz: BMat, dz_t: BMat,
+                     colsum: torch.Tensor) -> None:
+    M, N = x.shape
+    check(_lib.lib().psb_mse_sigmoid_grad(
+        y.data_ptr(), y.stride(0), x.data_ptr(), x.stride(0), M, N, loss.data_ptr(),
+        _ptr(dz), dz.ld if dz is not None else 0, _ptr(dz_t), dz_t.ld if dz_t is not None else 0,
+        _ptr(colsum), current_stream_ptr()), "psb_mse_sigmoid_grad")
+
+
+def gan_loss_grad(logit: torch.Tensor, B: int, losses: torch.Tensor, d_disc: BMat, d_disc_t: BMat,
+                  d_gen: BMat, db_disc_out: Optional[torch.Tensor]) -> None:
+    check(_lib.lib().psb_gan_loss_grad(
+        logit.data_ptr(), logit.stride(0), B, losses.data_ptr(), d_disc.ptr, d_disc.ld, d_disc_t.ptr,
+        d_gen.ptr, d_gen.ld, _ptr(db_disc_out), current_stream_ptr()), "psb_gan_loss_grad")
+
+
+def softmax_xent_grad(logits: torch.Tensor, labels: torch.Tensor, loss: torch.Tensor,
+                      dz: Optional[BMat], dz_t: Optional[BMat], colsum: Optional[torch.Tensor],
+                      correct: Optional[torch.Tensor] = None) -> None:
+    B, C = logits.shape
+    check(_lib.lib().psb_softmax_xent_grad(
+        logits.data_ptr(), logits.stride(0), labels.data_ptr(), labels.stride(0), B, C,
+        loss.data_ptr(), _ptr(dz), dz.ld if dz is not None else 0,
+        _ptr(dz_t), dz_t.ld if dz_t is not None else 0, _ptr(colsum), _ptr(correct),
+        current_stream_ptr()), "psb_softmax_xent_grad")

@@ -66,6 +66,109 @@ typedef struct psb_epilogue {
 int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const psb_epilogue_t* epi, int block_n /*0 = auto*/, void* stream);
 
+
+/* ------------------------------------------------------------------ persistent LSTM (H = 128)
+ * Forward: BasicLSTMCell unrolled over T steps from a zero state, one CTA per 16 batch rows,
+ * cell kernel resident in shared memory, gate GEMM on tcgen05 with the batch slice as the MMA
+ * N dimension, sigmoid/tanh pointwise on the TMEM accumulator, h fed back through shared
+ * memory.  `wt` is the cell kernel TRANSPOSED, bf16 [4H, ld_wt] (gate order i,j,f,o); it may
+ * point into a peer GPU's memory (the parameter pull is then part of this kernel).
+ * Optional outputs: h_last bf16 [B, ld_h], h_last_t bf16 [H, ld_ht]; for training also
+ * gates bf16 [T,4,B,H] (activated), c_all fp32 [T,B,H], xh_t bf16 [I+H, ld_xht] whose
+ * column t*B+b holds [x_t, h_{t-1}] of batch row b (the weight-gradient GEMM's A operand).
+ * ref: rnn.BasicLSTMCell(128, forget_bias=1.0) + rnn.static_rnn, lstm:50-52. */
+int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const float* bias, float forget_bias,
+                 int B, int T, int I, int H, void* h_last, int ld_h, void* h_last_t, int ld_ht,
+                 void* gates, float* c_all, void* xh_t, int ld_xht, void* stream);
+
+/* BPTT for psb_lstm_fwd when only the last hidden state feeds the loss.  `w` is the cell kernel
+ * in its natural layout, bf16 [I+H, ld_w]; dh_last fp32 [B, ld_dh].  Writes the gate gradients
+ * transposed, dg_t bf16 [4H, ld_dgt] (column t*B+b), and atomically adds the bias gradient into
+ * dbias fp32 [4H].  The kernel gradient is then one GEMM: dK = xh_t * dg_t^T (psb_gemm_bf16).
+ * ref: the gradient graph optimizer.minimize builds for static_rnn, lstm:97. */
+int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const void* gates,
+                 const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
+                 float* dbias, void* stream);
+
+/* ------------------------------------------------------------------ input cast, losses
+ * fp32 [M,N] -> bf16 [M, ld_out] (zero pad columns) and/or its transpose bf16 [N, ld_t].
+ * ref: feed_dict of the float32 placeholders, encoder:165, gan:192-194, lstm:128. */
+int psb_cast_transpose(const float* in, int ld_in, int M, int N, void* out, int ld_out,
+                       void* out_t, int ld_t, void* stream);
+
+/* MSE between the sigmoid output y (fp32 [M, ld_y]) and the target x (fp32 [M, ld_x]):
+ * *loss += mean((x-y)^2) (caller zeroes it), dz = dLoss/d(pre-activation) as bf16 [M, ld_dz],
+ * bf16 transposed [N, ld_dzt] and fp32 column sums (+=).  ref: encoder:131-135. */
+int psb_mse_sigmoid_grad(const float* y, int ld_y, const float* x, int ld_x, int M, int N,
+                         float* loss, void* dz, int ld_dz, void* dz_t, int ld_dzt,
+                         float* colsum, void* stream);
+
+/* GAN log-losses from discriminator logits (fp32, 2B rows with stride ld: real then fake).
+ * losses[0] = -mean(log D(G(z))), losses[1] = -mean(log D(x) + log(1 - D(G(z)))) (stable
+ * softplus form); d_disc bf16 [2B, ld_d] and d_disc_t bf16 [1, 2B] = d disc_loss / d logit;
+ * d_gen bf16 [B, ld_g] = d gen_loss / d logit_fake; *db_disc_out = sum(d_disc).
+ * ref: gan:142-143. */
+int psb_gan_loss_grad(const float* logit, int ld, int B, float* losses, void* d_disc, int ld_d,
+                      void* d_disc_t, void* d_gen, int ld_g, float* db_disc_out, void* stream);
+
+/* Mean softmax cross-entropy of logits fp32 [B,C] against labels fp32 [B,C] (C <= 32):
+ * *loss (overwritten), dz bf16 [B, ld_dz], dz_t bf16 [C, ld_dzt], colsum fp32 [C] (+=), and
+ * optionally *correct = number of rows whose argmax matches.  ref: lstm:92-94,99-100. */
+int psb_softmax_xent_grad(const float* logits, int ld, const float* labels, int ld_l, int B, int C,
+                          float* loss, void* dz, int ld_dz, void* dz_t, int ld_dzt, float* colsum,
+                          float* correct, void* stream);
+
+/* ------------------------------------------------------------------ fused gradient push
+ * One variable (or one contiguous run of it) owned by the calling rank. */
+typedef struct psb_push_seg {
+    uint64_t grad_offset;   /* element offset inside every rank's flat fp32 gradient buffer */
+    uint32_t numel;
+    uint32_t cols;          /* logical [numel/cols, cols] view used for the bf16 copies */
+    int32_t opt_kind;       /* 0 SGD, 1 RMSProp, 2 Adam */
+    float lr, h1, h2, eps;  /* h1 = decay | beta1, h2 = momentum | beta2 */
+    float* master;          /* fp32 [numel] master weights (owner memory; peer pointer in async mode) */
+    float* slot0;           /* rms | m */
+    float* slot1;           /* momentum | v */
+    const float* beta_pow;  /* Adam: {beta1^t, beta2^t} */
+    int64_t w_off;          /* element offset of the natural bf16 copy [rows, ld_w] in the arena, -1 = none */
+    int32_t ld_w;
+    int64_t wt_off;         /* element offset of the transposed bf16 copy [cols, ld_wt], -1 = none */
+    int32_t ld_wt;
+    int32_t home;           /* index into arena_ptrs that receives the copies when !bcast */
+    int32_t bcast;          /* 1: write the copies into every rank's arena (push-mode all-gather) */
+} psb_push_seg_t;
+
+typedef struct psb_beta_update {
+    float* beta_pow;        /* {beta1_power, beta2_power} */
+    float beta1, beta2;
+} psb_beta_update_t;
+
+typedef struct psb_push_desc {
+    const psb_push_seg_t* segs;      /* DEVICE array */
+    int nseg;
+    const float* const* grad_ptrs;   /* DEVICE array [world]: every rank's gradient buffer */
+    void* const* arena_ptrs;         /* DEVICE array [world]: every rank's bf16 arena */
+    uint32_t* const* pad_ptrs;       /* DEVICE array [world]: every rank's signal pad (>= 32 words) */
+    int world, rank;
+    float inv_replicas;              /* 1 / replicas_to_aggregate */
+    uint32_t step_id;                /* monotone token, first call = 1 */
+    uint32_t* local_ctrl;            /* DEVICE, 2 zero-initialised words private to this rank */
+    psb_beta_update_t beta[2];
+    int nbeta;
+    int32_t* global_step;            /* incremented by step_delta by the last block (NULL = not here) */
+    int step_delta;
+    int async_sgd_atomic;
+    int signal_params;               /* publish (and wait for) params-ready on the pads */
+    int blocks_per_seg;              /* 0 = default */
+} psb_push_desc_t;
+
+/* Reduce-scatter + optimizer apply (+ all-gather of the bf16 copies) in one kernel over peer
+ * memory; see csrc/push.cu.  Allocates nothing.
+ * ref: minimize() -> Apply* on the ps + AssignAdd(global_step), encoder:137 gan:158-159 lstm:97. */
+int psb_push_apply(const psb_push_desc_t* desc, void* stream);
+/* Block the stream until every rank has published params-ready >= step_id on `pad`. */
+int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
