@@ -37,11 +37,13 @@ struct PushArgs {
     int nseg;
     const float* const* grad_ptrs;     // [world]
     void* const* arena_ptrs;           // [world] bf16 arenas
+    float* const* farena_ptrs;         // [world] fp32 arenas (bias copies)
     uint32_t* const* pad_ptrs;         // [world]
     int world, rank;
+    int n_arenas;                      // entries of arena_ptrs/farena_ptrs written when bcast
     float inv_replicas;
-    uint32_t step_id;
-    uint32_t* local_ctrl;              // [0] go flag, [1] finished-block counter
+    uint32_t step_id;                  // 0 = take local_ctrl[2] + 1
+    uint32_t* local_ctrl;              // [0] go flag, [1] finished-block counter, [2] last step id
     psb_beta_update_t beta[2];
     int nbeta;
     int32_t* global_step;
@@ -70,6 +72,7 @@ struct OptCtx {
 };
 
 __device__ __forceinline__ float apply_one(const OptCtx& o, float w, float g, float* s0, float* s1, size_t i) {
+    if (o.kind < 0) return w;                 // refresh the compute copies only
     if (o.kind == 0) return w - o.lr * g;
     if (o.kind == 1) {
         float ms = s0[i], mom = s1[i];
@@ -91,6 +94,8 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
     const int tid = threadIdx.x;
     const bool first_block = blockIdx.x == 0 && blockIdx.y == 0;
     const uint32_t total_blocks = gridDim.x * gridDim.y;
+    const bool auto_step = a.step_id == 0;
+    if (auto_step) a.step_id = *reinterpret_cast<volatile uint32_t*>(a.local_ctrl + 2) + 1;
 
     // ---------------- cross-GPU: all gradients of this step are in place
     if (a.world > 1) {
@@ -133,7 +138,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
         const bool vec = (s.numel % 4 == 0) && (s.grad_offset % 4 == 0) && (cols % 4 == 0) &&
                          ((reinterpret_cast<uintptr_t>(master) & 15) == 0) &&
                          !(a.async_sgd_atomic && s.opt_kind == 0);
-        const int n_dst = s.bcast ? a.world : 1;
+        const int n_dst = s.bcast ? a.n_arenas : 1;
         const uint32_t stride = gridDim.x * kPushThreads;
         if (vec) {
             for (uint32_t i4 = blockIdx.x * kPushThreads + tid; i4 < s.numel / 4; i4 += stride) {
@@ -161,6 +166,8 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                         pk.y = *reinterpret_cast<const uint32_t*>(&hi);
                         *reinterpret_cast<uint2*>(p) = pk;
                     }
+                    if (s.f_off >= 0)
+                        *reinterpret_cast<float4*>(a.farena_ptrs[s.bcast ? d : s.home] + s.f_off + i) = w;
                     if (s.wt_off >= 0) {
                         __nv_bfloat16* p = arena + s.wt_off + static_cast<size_t>(col) * s.ld_wt + row;
                         p[0] = lo.x;
@@ -187,6 +194,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                 for (int d = 0; d < n_dst; ++d) {
                     __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
                     if (s.w_off >= 0) arena[s.w_off + static_cast<size_t>(row) * s.ld_w + col] = wb;
+                    if (s.f_off >= 0) a.farena_ptrs[s.bcast ? d : s.home][s.f_off + i] = w;
                     if (s.wt_off >= 0) arena[s.wt_off + static_cast<size_t>(col) * s.ld_wt + row] = wb;
                 }
             }
@@ -205,6 +213,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
     if (is_last) {
         if (tid == 0) {
             a.local_ctrl[1] = 0;
+            if (auto_step) a.local_ctrl[2] = a.step_id;
             for (int k = 0; k < a.nbeta; ++k) {
                 a.beta[k].beta_pow[0] *= a.beta[k].beta1;
                 a.beta[k].beta_pow[1] *= a.beta[k].beta2;
@@ -241,12 +250,12 @@ extern "C" int psb_push_apply(const psb_push_desc_t* d, void* stream) {
     if (d->world < 1 || d->world > 16 || d->rank < 0 || d->rank >= d->world)
         return fail(PSB_ERR_ARG, "psb_push_apply: world must be 1..16 and 0 <= rank < world");
     if (d->nseg < 0 || (d->nseg > 0 && !d->segs)) return fail(PSB_ERR_ARG, "psb_push_apply: bad segment table");
-    if (!d->grad_ptrs || !d->arena_ptrs || !d->local_ctrl) return fail(PSB_ERR_ARG, "psb_push_apply: null table");
+    if (!d->grad_ptrs || !d->arena_ptrs || !d->farena_ptrs || !d->local_ctrl) return fail(PSB_ERR_ARG, "psb_push_apply: null table");
     if (d->world > 1 && !d->pad_ptrs) return fail(PSB_ERR_ARG, "psb_push_apply: world > 1 needs signal pads");
     if (d->nbeta < 0 || d->nbeta > 2) return fail(PSB_ERR_ARG, "psb_push_apply: at most two Adam optimizers");
     PushArgs a;
     a.segs = d->segs; a.nseg = d->nseg; a.grad_ptrs = d->grad_ptrs; a.arena_ptrs = d->arena_ptrs;
-    a.pad_ptrs = d->pad_ptrs; a.world = d->world; a.rank = d->rank; a.inv_replicas = d->inv_replicas;
+    a.farena_ptrs = d->farena_ptrs; a.pad_ptrs = d->pad_ptrs; a.world = d->world; a.rank = d->rank; a.n_arenas = d->n_arenas > 0 ? d->n_arenas : d->world; a.inv_replicas = d->inv_replicas;
     a.step_id = d->step_id; a.local_ctrl = d->local_ctrl;
     a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
     a.global_step = d->global_step; a.step_delta = d->step_delta;

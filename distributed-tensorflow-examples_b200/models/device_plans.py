@@ -1,0 +1,234 @@
+"""Device execution plans: the three models as fixed sequences of sm_100a kernels.
+
+A plan owns every activation / gradient-of-activation buffer (allocated once), reads the
+bf16/fp32 compute copies of the parameters from the :class:`~psb200.store.nvl.NvlStore`
+arena and leaves the fp32 parameter gradients in the store's flat gradient buffer.  No
+allocation and no host synchronisation happens inside ``forward_backward`` — the trainer
+captures it (plus the gradient push) into one CUDA graph.
+
+Layout rules every plan follows (all GEMM operands are K-major bf16):
+  forward   Y[B,N]  = act(X[B,K] Wt[N,K]^T + b)       -> Y and Y^T
+  dgrad     dX[B,K] = (dZ[B,N] W[K,N]^T) * act'(X)    -> dZ_prev and dZ_prev^T, db via colsum
+  wgrad     dW[K,N] = X^T[K,B] dZ^T[N,B]^T            -> fp32 into the gradient buffer
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from ..ops import cuda as K
+from ..ops.cuda import ACT_NONE, ACT_RELU, ACT_SIGMOID, BMat
+from ..store.nvl import NvlStore
+from . import encoder as enc_mod
+from . import gan as gan_mod
+from . import lstm as lstm_mod
+
+
+class DevicePlan:
+    """Common surface: static input tensors, ``forward_backward()``, result tensors."""
+
+    inputs: Dict[str, torch.Tensor]
+    losses: Dict[str, torch.Tensor]
+
+    def __init__(self, model, store: NvlStore, batch: int):
+        self.model, self.store, self.B = model, store, batch
+        self.dev = store.device
+        self.inputs = {}
+        self.losses = {}
+
+    def _name(self, key: str) -> str:
+        return self.model.var[key].name
+
+    def forward_backward(self) -> None:
+        raise NotImplementedError
+
+    def forward(self) -> None:
+        """Inference-only pass (LSTM accuracy)."""
+        raise NotImplementedError
+
+    def kernels_per_step(self) -> int:
+        raise NotImplementedError
+
+
+class EncoderPlan(DevicePlan):
+    """``encoder:67-85,128-137`` — 4 fused dense+sigmoid forward GEMMs, MSE kernel, 4 wgrad and
+    3 dgrad GEMMs (sigmoid' and bias-gradient fused in their epilogues)."""
+
+    def __init__(self, model, store, batch=enc_mod.batch_size):
+        super().__init__(model, store, batch)
+        B, dev = batch, self.dev
+        dims = [enc_mod.num_input, enc_mod.num_hidden_1, enc_mod.num_hidden_2, enc_mod.num_hidden_1,
+                enc_mod.num_input]
+        self.dims = dims
+        self.inputs["x"] = torch.zeros(B, dims[0], device=dev)
+        self.act = [BMat(B, dims[0], dev)] + [BMat(B, d, dev) for d in dims[1:4]]
+        self.act_t = [BMat(d, B, dev) for d in dims[0:4]]
+        self.y = torch.zeros(B, dims[4], device=dev)
+        self.dz = [None] + [BMat(B, d, dev) for d in dims[1:]]        # dz[l] = grad at output of layer l
+        self.dz_t = [None] + [BMat(d, B, dev) for d in dims[1:]]
+        self.losses["loss"] = torch.zeros((), device=dev)
+        self.wkeys = [w for w, _ in enc_mod.LAYERS]
+        self.bkeys = [b for _, b in enc_mod.LAYERS]
+
+    def forward(self, need_t: bool = True) -> None:
+        s, n = self.store, self._name
+        K.cast_transpose(self.inputs["x"], self.act[0], self.act_t[0] if need_t else None)
+        for l in range(3):
+            K.gemm(self.act[l], s.wt(n(self.wkeys[l])), bias=s.vec(n(self.bkeys[l])), act=ACT_SIGMOID,
+                   out=self.act[l + 1], out_t=self.act_t[l + 1] if need_t else None)
+        K.gemm(self.act[3], s.wt(n(self.wkeys[3])), bias=s.vec(n(self.bkeys[3])), act=ACT_SIGMOID,
+               out_f32=self.y)
+
+    def forward_backward(self) -> None:
+        s, n = self.store, self._name
+        s.zero_grads()
+        self.losses["loss"].zero_()
+        self.forward()
+        K.mse_sigmoid_grad(self.y, self.inputs["x"], self.losses["loss"], self.dz[4], self.dz_t[4],
+                           s.grad(n(self.bkeys[3])))
+        for l in range(3, -1, -1):
+            # dW_l = act_{l}^T dz_{l+1}
+            K.gemm(self.act_t[l], self.dz_t[l + 1], out_f32=s.grad(n(self.wkeys[l])))
+            if l > 0:
+                K.gemm(self.dz[l + 1], s.w(n(self.wkeys[l])), yprev=self.act[l], dact=1,
+                       out=self.dz[l], out_t=self.dz_t[l], colsum=s.grad(n(self.bkeys[l - 1])))
+
+    def kernels_per_step(self) -> int:
+        return 1 + 4 + 1 + 4 + 3
+
+
+class GanPlan(DevicePlan):
+    """``gan:76-93,139-159`` — G forward, D forward on [real; fake] in one batch of 2B rows, the
+    fused log-loss kernel, then the discriminator-variable path and the generator-variable path
+    (through D) as dgrad/wgrad GEMMs."""
+
+    def __init__(self, model, store, batch=gan_mod.batch_size, device_noise: bool = True, seed: int = 0):
+        super().__init__(model, store, batch)
+        B, dev = batch, self.dev
+        nz, gh, im, dh = gan_mod.noise_dim, gan_mod.gen_hidden_dim, gan_mod.image_dim, gan_mod.disc_hidden_dim
+        self.device_noise, self.seed = device_noise, seed
+        self.noise_counter = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.inputs["x"] = torch.zeros(B, im, device=dev)
+        self.inputs["z"] = torch.zeros(B, nz, device=dev)
+        self.Z, self.ZT = BMat(B, nz, dev), BMat(nz, B, dev)
+        self.GH, self.GHT = BMat(B, gh, dev), BMat(gh, B, dev)
+        self.Din, self.DinT = BMat(2 * B, im, dev), BMat(im, 2 * B, dev)
+        self.DH, self.DHT = BMat(2 * B, dh, dev), BMat(dh, 2 * B, dev)
+        self.logit = torch.zeros(2 * B, 1, device=dev)
+        self.losses_t = torch.zeros(2, device=dev)
+        self.losses["gen_loss"], self.losses["disc_loss"] = self.losses_t[0], self.losses_t[1]
+        self.d_disc, self.d_disc_t, self.d_gen = BMat(2 * B, 1, dev), BMat(1, 2 * B, dev), BMat(B, 1, dev)
+        self.dZ1, self.dZ1T = BMat(2 * B, dh, dev), BMat(dh, 2 * B, dev)
+        self.dZ1f = BMat(B, dh, dev)
+        self.dZo, self.dZoT = BMat(B, im, dev), BMat(im, B, dev)
+        self.dZh, self.dZhT = BMat(B, gh, dev), BMat(gh, B, dev)
+        # views of the fake half
+        self.Din_fake, self.DinT_fake = self.Din.rows_view(B, 2 * B), self.DinT.cols_view(B, 2 * B)
+        self.Din_real, self.DinT_real = self.Din.rows_view(0, B), self.DinT.cols_view(0, B)
+        self.DH_fake = self.DH.rows_view(B, 2 * B)
+
+    def forward(self) -> None:
+        s, n, B = self.store, self._name, self.B
+        K.cast_transpose(self.inputs["x"], self.Din_real, self.DinT_real)
+        if self.device_noise:
+            K.uniform_noise(B, gan_mod.noise_dim, -1.0, 1.0, self.seed + 7919 * s.rank,
+                            self.noise_counter, out=self.inputs["z"], out_bf16=self.Z, out_t=self.ZT)
+        else:
+            K.cast_transpose(self.inputs["z"], self.Z, self.ZT)
+        K.gemm(self.Z, s.wt(n("w_gen_hidden1")), bias=s.vec(n("b_gen_hidden1")), act=ACT_RELU,
+               out=self.GH, out_t=self.GHT)
+        K.gemm(self.GH, s.wt(n("w_gen_out")), bias=s.vec(n("b_gen_out")), act=ACT_SIGMOID,
+               out=self.Din_fake, out_t=self.DinT_fake)
+        K.gemm(self.Din, s.wt(n("w_disc_hidden1")), bias=s.vec(n("b_disc_hidden1")), act=ACT_RELU,
+               out=self.DH, out_t=self.DHT)
+        K.gemm(self.DH, s.wt(n("w_disc_out")), bias=s.vec(n("b_disc_out")), act=ACT_NONE,
+               out_f32=self.logit)
+
+    def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
+        s, n, B = self.store, self._name, self.B
+        s.zero_grads()
+        self.forward()
+        K.gan_loss_grad(self.logit, B, self.losses_t, self.d_disc, self.d_disc_t, self.d_gen,
+                        s.grad(n("b_disc_out")) if disc else None)
+        if disc:
+            K.gemm(self.DHT, self.d_disc_t, out_f32=s.grad(n("w_disc_out")))
+            K.gemm(self.d_disc, s.w(n("w_disc_out")), yprev=self.DH, dact=2, out=self.dZ1, out_t=self.dZ1T,
+                   colsum=s.grad(n("b_disc_hidden1")))
+            K.gemm(self.DinT, self.dZ1T, out_f32=s.grad(n("w_disc_hidden1")))
+        if gen:
+            K.gemm(self.d_gen, s.w(n("w_disc_out")), yprev=self.DH_fake, dact=2, out=self.dZ1f)
+            K.gemm(self.dZ1f, s.w(n("w_disc_hidden1")), yprev=self.Din_fake, dact=1, out=self.dZo,
+                   out_t=self.dZoT, colsum=s.grad(n("b_gen_out")))
+            K.gemm(self.GHT, self.dZoT, out_f32=s.grad(n("w_gen_out")))
+            K.gemm(self.dZo, s.w(n("w_gen_out")), yprev=self.GH, dact=2, out=self.dZh, out_t=self.dZhT,
+                   colsum=s.grad(n("b_gen_hidden1")))
+            K.gemm(self.ZT, self.dZhT, out_f32=s.grad(n("w_gen_hidden1")))
+
+    def kernels_per_step(self) -> int:
+        return 2 + 4 + 1 + 3 + 5
+
+
+class LstmPlan(DevicePlan):
+    """``lstm:49-53,89-100`` — persistent LSTM forward kernel, head GEMM, fused softmax-CE,
+    head wgrad/dgrad GEMMs, persistent BPTT kernel, one big wgrad GEMM for the cell kernel."""
+
+    def __init__(self, model, store, batch=lstm_mod.batch_size, pull_from_owner: bool = False):
+        super().__init__(model, store, batch)
+        B, dev = batch, self.dev
+        T, I, H, C = model.T, model.I, model.H, model.C
+        self.inputs["x"] = torch.zeros(B, T, I, device=dev)
+        self.inputs["y"] = torch.zeros(B, C, device=dev)
+        self.h_last, self.h_last_t = BMat(B, H, dev), BMat(H, B, dev)
+        self.saved = K.LstmSaved(B, T, I, H, dev)
+        self.logits = torch.zeros(B, C, device=dev)
+        self.losses["loss"] = torch.zeros((), device=dev)
+        self.correct = torch.zeros((), device=dev)
+        self.dlogits, self.dlogits_t = BMat(B, C, dev), BMat(C, B, dev)
+        self.dh = torch.zeros(B, H, device=dev)
+        # bcast=False stores keep the cell kernel only in its owner's arena: the LSTM kernels
+        # then read it through the owner's peer pointer (pull fused into the consumer)
+        self.pull_from_owner = pull_from_owner
+        kname = self._name("kernel")
+        self._k_owner = store.owner(kname) if pull_from_owner else None
+
+    def _kernel_ptrs(self):
+        s, kname = self.store, self._name("kernel")
+        if self._k_owner is None:
+            return None, None
+        return s.wt(kname, self._k_owner).ptr, s.w(kname, self._k_owner).ptr
+
+    def forward(self, train: bool = False) -> None:
+        s, n = self.store, self._name
+        wt_ptr, _ = self._kernel_ptrs()
+        K.lstm_fwd(self.inputs["x"], s.wt(n("kernel")), s.vec(n("bias")), lstm_mod.forget_bias,
+                   self.h_last, self.h_last_t if train else None, self.saved if train else None,
+                   wt_ptr=wt_ptr)
+        K.gemm(self.h_last, s.wt(n("out_w")), bias=s.vec(n("out_b")), out_f32=self.logits)
+
+    def evaluate(self) -> None:
+        """Fills ``losses['loss']`` and ``correct`` for the current inputs without touching
+        gradients (``sess.run(accuracy, ...)``, ``lstm:134-138``)."""
+        self.forward(train=False)
+        K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], None, None, None,
+                            self.correct)
+
+    def forward_backward(self) -> None:
+        s, n = self.store, self._name
+        _, w_ptr = self._kernel_ptrs()
+        s.zero_grads()
+        self.forward(train=True)
+        K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
+                            self.dlogits_t, s.grad(n("out_b")), self.correct)
+        K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
+        K.gemm(self.dlogits, s.w(n("out_w")), out_f32=self.dh)
+        K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
+        K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")))
+
+    def kernels_per_step(self) -> int:
+        return 7
+
+
+def make_plan(model, store: NvlStore, batch: Optional[int] = None, **kw) -> DevicePlan:
+    cls = {"encoder": EncoderPlan, "gan": GanPlan, "lstm": LstmPlan}[model.name]
+    return cls(model, store, batch or model.batch_size, **kw)

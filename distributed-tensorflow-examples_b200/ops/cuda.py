@@ -6,6 +6,7 @@ padded leading dimension (:class:`BMat`), accumulators/gradients/master weights 
 """
 from __future__ import annotations
 
+import ctypes
 from typing import Optional
 
 import torch
@@ -37,7 +38,21 @@ class BMat:
 
     @property
     def ld(self) -> int:
-        return self.t.shape[1]
+        return self.t.stride(0)
+
+    def rows_view(self, r0: int, r1: int) -> "BMat":
+        """Rows ``r0:r1`` as a matrix sharing this storage."""
+        m = BMat.__new__(BMat)
+        m.rows, m.cols, m.t = r1 - r0, self.cols, self.t[r0:r1]
+        return m
+
+    def cols_view(self, c0: int, c1: int) -> "BMat":
+        """Columns ``c0:c1`` (c0 a multiple of 8) as a matrix sharing this storage."""
+        if c0 % 8:
+            raise ValueError("column views must start on a 16-byte boundary")
+        m = BMat.__new__(BMat)
+        m.rows, m.cols, m.t = self.rows, c1 - c0, self.t[:, c0:]
+        return m
 
     @property
     def ptr(self) -> int:
@@ -45,6 +60,12 @@ class BMat:
 
     def float(self) -> torch.Tensor:
         return self.t[:, : self.cols].float()
+
+    @staticmethod
+    def wrap(t: torch.Tensor, rows: int, cols: int) -> "BMat":
+        m = BMat.__new__(BMat)
+        m.rows, m.cols, m.t = rows, cols, t
+        return m
 
     @staticmethod
     def from_tensor(x: torch.Tensor) -> "BMat":
@@ -189,3 +210,18 @@ def softmax_xent_grad(logits: torch.Tensor, labels: torch.Tensor, loss: torch.Te
         loss.data_ptr(), _ptr(dz), dz.ld if dz is not None else 0,
         _ptr(dz_t), dz_t.ld if dz_t is not None else 0, _ptr(colsum), _ptr(correct),
         current_stream_ptr()), "psb_softmax_xent_grad")
+
+
+_lib.register_signature("psb_uniform_noise", [c_void_p, c_int, c_int, c_int, c_float, c_float,
+                                              ctypes.c_uint32, c_void_p, c_void_p, c_int, c_void_p,
+                                              c_int, c_void_p])
+
+
+def uniform_noise(rows: int, cols: int, lo: float, hi: float, seed: int,
+                  step_counter: Optional[torch.Tensor], out: Optional[torch.Tensor] = None,
+                  out_bf16: Optional[BMat] = None, out_t: Optional[BMat] = None) -> None:
+    """U(lo,hi) noise generated on the device (``np.random.uniform`` of ``gan:189``)."""
+    check(_lib.lib().psb_uniform_noise(
+        _ptr(out), rows, cols, out.stride(0) if out is not None else 0, lo, hi, seed & 0xFFFFFFFF,
+        _ptr(step_counter), _ptr(out_bf16), out_bf16.ld if out_bf16 is not None else 0,
+        _ptr(out_t), out_t.ld if out_t is not None else 0, current_stream_ptr()), "psb_uniform_noise")

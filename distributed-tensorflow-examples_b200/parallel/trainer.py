@@ -1,0 +1,158 @@
+"""GPU training engine: one process per B200, the whole step as one CUDA graph.
+
+``DeviceTrainer`` is the public API a user (and ``bench.py``) drives:
+
+    tr = DeviceTrainer("lstm", rank, world, group, mode="sync")
+    tr.initialize()                       # chief init_op (or restore) + first parameter pull
+    out = tr.step({"x": x_pinned, "y": y_pinned})     # H2D, graph replay, loss D2H
+
+One step = the model's device plan (forward, losses, backward: hand-written sm_100a
+kernels) followed by the fused gradient push (reduce-scatter + optimizer + all-gather in
+one kernel over NVLink peer memory).  It plays the role of one ``sess.run([train_op, loss,
+global_step], feed_dict=...)`` of the reference (``encoder:165``, ``gan:193``,
+``lstm:128``).
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from ..models import make_model
+from ..models.device_plans import make_plan
+from ..ops import _lib
+from ..placement import VariableRegistry, replica_device_setter
+from ..store.nvl import NvlStore
+
+
+class DeviceTrainer:
+    def __init__(self, model_name: str, rank: int = 0, world: int = 1, group=None, mode: str = "sync",
+                 batch: Optional[int] = None, seed: int = 0, use_graph: bool = True,
+                 gan_update: str = "simultaneous", bcast: bool = True, plan_kwargs: Optional[dict] = None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("DeviceTrainer needs a CUDA device; the CPU path is psb200.session.Session")
+        _lib.lib()   # fail loudly if the kernel library is missing
+        self.rank, self.world, self.group, self.mode, self.seed = rank, world, group, mode, seed
+        self.registry = VariableRegistry(replica_device_setter(
+            worker_device="/job:worker/task:%d" % rank, ps_tasks=world))
+        self.model = make_model(model_name).build(self.registry)
+        self.store = NvlStore(self.model, self.registry, rank, world, group, mode=mode, bcast=bcast)
+        kw = dict(plan_kwargs or {})
+        if self.model.name == "gan":
+            kw.setdefault("seed", seed)
+        self.plan = make_plan(self.model, self.store, batch, **kw)
+        self.batch = self.plan.B
+        self.gan_update = gan_update if self.model.name == "gan" else "simultaneous"
+        self.use_graph = use_graph
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._loss_keys = list(self.plan.losses.keys())
+        self._host_losses = torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory()
+        self._host_step = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._dev_losses = torch.zeros(len(self._loss_keys), device=self.store.device)
+        self.local_step = 0
+        self._launches_per_step = 0
+
+    # ------------------------------------------------------------------ lifecycle
+    def initialize(self, values: Optional[Dict[str, torch.Tensor]] = None) -> None:
+        """``init_op`` (or a restored checkpoint) -> owners' state, then the first pull.
+        Collective: every rank calls it; all ranks derive identical values from ``seed``."""
+        if self.graph is None and self.use_graph:
+            self._warm_up()
+        if values is None:
+            values = self.registry.initial_values(self.seed)
+        self.store.assign(values)
+        self._barrier()
+        self.store.refresh_copies()
+        self._barrier()
+        if self.use_graph and self.graph is None:
+            self._capture()
+
+    def _barrier(self) -> None:
+        torch.cuda.synchronize()
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)
+
+    def _enqueue_step(self) -> None:
+        if self.gan_update == "alternating":
+            self.plan.forward_backward(disc=True, gen=False)
+            self.store.push(["train_disc"])
+            self.plan.forward_backward(disc=False, gen=True)
+            self.store.push(["train_gen"])
+        else:
+            self.plan.forward_backward()
+            self.store.push()
+        for i, k in enumerate(self._loss_keys):
+            self._dev_losses[i:i + 1].copy_(self.plan.losses[k].reshape(1))
+
+    def _warm_up(self) -> None:
+        """One eager step on scratch state: sets kernel attributes, fills the TMA descriptor
+        cache, and proves the launch sequence before it is captured."""
+        before = _lib.launch_count()
+        self._enqueue_step()
+        self._launches_per_step = _lib.launch_count() - before
+        self._barrier()
+
+    def _capture(self) -> None:
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._enqueue_step()
+        self.graph = g
+        torch.cuda.synchronize()
+
+    # ------------------------------------------------------------------ stepping
+    def launches_per_step(self) -> int:
+        """Number of this library's kernels in one training step."""
+        return self._launches_per_step
+
+    def step_device(self) -> None:
+        """Run one step on whatever is in the plan's static input buffers (no H2D, no sync)."""
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._enqueue_step()
+        self.local_step += 1
+
+    def step(self, batch: Dict[str, torch.Tensor]) -> Dict[str, float]:
+        """One training step end to end: H2D of the batch, the step, D2H of losses and
+        ``global_step``."""
+        for k, v in batch.items():
+            if k in self.plan.inputs:
+                self.plan.inputs[k].copy_(v.reshape(self.plan.inputs[k].shape), non_blocking=True)
+        self.step_device()
+        self._host_losses.copy_(self._dev_losses, non_blocking=True)
+        gs_rank = self.store.gs_owner if self.mode == "async" else self.rank
+        self._host_step.copy_(self.store.heap.tensor(self.store._gs_off, (1,), torch.int32, gs_rank),
+                              non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        out = {k: float(self._host_losses[i]) for i, k in enumerate(self._loss_keys)}
+        out["global_step"] = int(self._host_step[0])
+        return out
+
+    def h2d_bytes_per_step(self, batch: Dict[str, torch.Tensor]) -> int:
+        return sum(v.numel() * v.element_size() for k, v in batch.items() if k in self.plan.inputs)
+
+    def d2h_bytes_per_step(self) -> int:
+        return self._host_losses.numel() * 4 + 4
+
+    def global_step(self) -> int:
+        return self.store.global_step()
+
+    # ------------------------------------------------------------------ evaluation / state
+    def accuracy(self, x: torch.Tensor, y: torch.Tensor) -> float:
+        """LSTM: fraction of ``x`` classified correctly (``lstm:99-100,134-138``)."""
+        if self.model.name != "lstm":
+            raise ValueError("accuracy is defined for the LSTM classifier only")
+        self.plan.inputs["x"].copy_(x.reshape(self.plan.inputs["x"].shape))
+        self.plan.inputs["y"].copy_(y)
+        self.plan.evaluate()
+        torch.cuda.synchronize()
+        return float(self.plan.correct.item()) / x.shape[0]
+
+    def variables(self) -> Dict[str, torch.Tensor]:
+        """Every checkpoint variable, read from its owner (CPU tensors keyed by SURVEY §2.4 names)."""
+        return self.store.read_all()
+
+    def close(self) -> None:
+        self.graph = None
+        self.store.close()

@@ -124,7 +124,7 @@ typedef struct psb_push_seg {
     uint64_t grad_offset;   /* element offset inside every rank's flat fp32 gradient buffer */
     uint32_t numel;
     uint32_t cols;          /* logical [numel/cols, cols] view used for the bf16 copies */
-    int32_t opt_kind;       /* 0 SGD, 1 RMSProp, 2 Adam */
+    int32_t opt_kind;       /* 0 SGD, 1 RMSProp, 2 Adam, -1 none (only refresh the copies) */
     float lr, h1, h2, eps;  /* h1 = decay | beta1, h2 = momentum | beta2 */
     float* master;          /* fp32 [numel] master weights (owner memory; peer pointer in async mode) */
     float* slot0;           /* rms | m */
@@ -134,6 +134,7 @@ typedef struct psb_push_seg {
     int32_t ld_w;
     int64_t wt_off;         /* element offset of the transposed bf16 copy [cols, ld_wt], -1 = none */
     int32_t ld_wt;
+    int64_t f_off;          /* element offset of an fp32 copy [numel] in the fp32 arena, -1 = none */
     int32_t home;           /* index into arena_ptrs that receives the copies when !bcast */
     int32_t bcast;          /* 1: write the copies into every rank's arena (push-mode all-gather) */
 } psb_push_seg_t;
@@ -148,11 +149,14 @@ typedef struct psb_push_desc {
     int nseg;
     const float* const* grad_ptrs;   /* DEVICE array [world]: every rank's gradient buffer */
     void* const* arena_ptrs;         /* DEVICE array [world]: every rank's bf16 arena */
+    float* const* farena_ptrs;       /* DEVICE array [world]: every rank's fp32 arena */
     uint32_t* const* pad_ptrs;       /* DEVICE array [world]: every rank's signal pad (>= 32 words) */
     int world, rank;
+    int n_arenas;                    /* arenas written when a segment has bcast=1 (0 = world) */
     float inv_replicas;              /* 1 / replicas_to_aggregate */
-    uint32_t step_id;                /* monotone token, first call = 1 */
-    uint32_t* local_ctrl;            /* DEVICE, 2 zero-initialised words private to this rank */
+    uint32_t step_id;                /* monotone token, first call = 1; 0 = use local_ctrl[2] + 1
+                                        (lets a captured CUDA graph replay the launch) */
+    uint32_t* local_ctrl;            /* DEVICE, 4 zero-initialised words private to this rank */
     psb_beta_update_t beta[2];
     int nbeta;
     int32_t* global_step;            /* incremented by step_delta by the last block (NULL = not here) */
@@ -168,6 +172,24 @@ typedef struct psb_push_desc {
 int psb_push_apply(const psb_push_desc_t* desc, void* stream);
 /* Block the stream until every rank has published params-ready >= step_id on `pad`. */
 int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream);
+
+/* ------------------------------------------------------------------ peer memory (CUDA IPC)
+ * psb_heap_alloc cudaMalloc's and zeroes one "symmetric heap" (THE allocating call of this
+ * library; every buffer the store uses is carved from it).  psb_ipc_export/psb_ipc_open move
+ * a 64-byte cudaIpcMemHandle_t between the ranks of one box so kernels can dereference peer
+ * pointers over NVLink.  ref: the ps<->worker gRPC edges set up at encoder:96-98,157. */
+int psb_heap_alloc(size_t bytes, void** out);
+int psb_heap_free(void* p);
+int psb_ipc_export(void* p, unsigned char* handle64);
+int psb_ipc_open(const unsigned char* handle64, void** out);
+int psb_ipc_close(void* p);
+
+/* U(lo,hi) noise [rows, cols] generated on the device from (seed, *step_counter, index); the
+ * kernel advances *step_counter by one, so a captured graph draws fresh noise on every replay.
+ * Any of the fp32 / bf16 / bf16-transposed outputs may be NULL.  ref: np.random.uniform at gan:189. */
+int psb_uniform_noise(float* out, int rows, int cols, int ld, float lo, float hi, uint32_t seed,
+                      uint32_t* step_counter, void* out_bf16, int ld_bf16, void* out_t,
+                      int ld_t, void* stream);
 
 #ifdef __cplusplus
 }
