@@ -1,0 +1,182 @@
+"""PyTorch DDP/NCCL rendition of the reference models — the fallback baseline BASELINE.json
+mandates because the TF-1.11 scripts cannot run on this image.
+
+Same architectures, same per-GPU batch, same optimizers and hyper-parameters as
+``encoder:45-51,137``, ``gan:50-57,146-159``, ``lstm:27-34,96``; idiomatic PyTorch: ``nn.Linear``
+(cuBLAS), ``nn.LSTM`` (cuDNN), bf16 autocast, ``DistributedDataParallel`` gradient all-reduce
+(NCCL), stock ``torch.optim`` optimizers.  Timed exactly like the product arm (``bench.py``).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+class AE(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.l = nn.ModuleList([nn.Linear(784, 256), nn.Linear(256, 128), nn.Linear(128, 256), nn.Linear(256, 784)])
+        for m in self.l:
+            nn.init.normal_(m.weight, std=1.0)
+            nn.init.normal_(m.bias, std=1.0)
+
+    def forward(self, x):
+        h = x
+        for m in self.l:
+            h = torch.sigmoid(m(h))
+        return ((x - h.float()) ** 2).mean()
+
+
+class LSTMNet(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.rnn = nn.LSTM(28, 128, batch_first=True)
+        self.head = nn.Linear(128, 10)
+
+    def forward(self, x, y):
+        out, _ = self.rnn(x)
+        logits = self.head(out[:, -1])
+        return F.cross_entropy(logits.float(), y.argmax(1))
+
+
+class G(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a, self.b = nn.Linear(100, 256), nn.Linear(256, 784)
+
+    def forward(self, z):
+        return torch.sigmoid(self.b(torch.relu(self.a(z))))
+
+
+class D(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a, self.b = nn.Linear(784, 256), nn.Linear(256, 1)
+
+    def forward(self, x):
+        return self.b(torch.relu(self.a(x)))       # logits
+
+
+def _wrap(m, world, local):
+    m = m.cuda()
+    if world > 1:
+        from torch.nn.parallel import DistributedDataParallel as DDP
+        m = DDP(m, device_ids=[local], gradient_as_bucket_view=True)
+    return m
+
+
+def build_step(model: str, world: int, local: int):
+    """Returns (step_fn(batch) -> loss tensor, input names)."""
+    if model == "encoder":
+        net = _wrap(AE(), world, local)
+        opt = torch.optim.RMSprop(net.parameters(), lr=0.01, alpha=0.9, eps=1e-10)
+
+        def step(b):
+            opt.zero_grad(set_to_none=True)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = net(b["x"])
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+    if model == "lstm":
+        net = _wrap(LSTMNet(), world, local)
+        opt = torch.optim.SGD(net.parameters(), lr=0.001)
+
+        def step(b):
+            opt.zero_grad(set_to_none=True)
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = net(b["x"], b["y"])
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+    g, d = _wrap(G(), world, local), _wrap(D(), world, local)
+    og = torch.optim.Adam(g.parameters(), lr=2e-4)
+    od = torch.optim.Adam(d.parameters(), lr=2e-4)
+
+    def step(b):
+        # both train ops from one forward pass, like gan:193
+        og.zero_grad(set_to_none=True)
+        od.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            fake = g(b["z"])
+            l_real = d(b["x"]).float()
+            l_fake = d(fake).float()
+            gen_loss = F.softplus(-l_fake).mean()
+            disc_loss = (F.softplus(-l_real) + F.softplus(l_fake)).mean()
+        g_params = [p for p in g.parameters()]
+        d_params = [p for p in d.parameters()]
+        gg = torch.autograd.grad(gen_loss, g_params, retain_graph=True)
+        gd = torch.autograd.grad(disc_loss, d_params)
+        for p, gr in zip(g_params, gg):
+            p.grad = gr
+        for p, gr in zip(d_params, gd):
+            p.grad = gr
+        if world > 1:
+            import torch.distributed as dist
+            flat = torch.cat([p.grad.reshape(-1) for p in g_params + d_params])
+            dist.all_reduce(flat)
+            flat /= world
+            o = 0
+            for p in g_params + d_params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p))
+                o += p.numel()
+        og.step()
+        od.step()
+        return gen_loss + disc_loss
+    return step
+
+
+def run(args, rank, world, local, bench):
+    model = args.model
+    B = bench.PER_GPU_BATCH[model]
+    step = build_step(model, world, local)
+    batches = bench.synthetic_batches(model, B, 8, args.seed * 1000 + rank)
+    dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    host_loss = torch.zeros(1).pin_memory()
+
+    def dev_step(i):
+        step(dev_batches[i % len(dev_batches)])
+
+    def e2e_step(i):
+        b = {k: v.cuda(non_blocking=True) for k, v in batches[i % len(batches)].items()}
+        loss = step(b)
+        host_loss.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for i in range(args.warmup):
+        dev_step(i)
+    torch.cuda.synchronize()
+    sampler = bench.ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = bench.timed_device_steps(dev_step, args.steps, world, flush)
+    for i in range(args.warmup):
+        e2e_step(i)
+    ms_e2e = bench.timed_e2e_steps(e2e_step, args.steps, world)
+    clocks = sampler.stop() if rank == 0 else None
+    res = None
+    if rank == 0:
+        total = B * world * args.steps
+        res = {"metric": "examples/sec", "value": round(total / (ms / 1e3), 1), "unit": "examples/s",
+               "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "bf16 autocast", "data": "synthetic MNIST-shaped, random-init weights",
+               "impl": "torch_ddp",
+               "config": {"model": bench.MODEL_LABEL[model], "global_batch": B * world,
+                          "parallelism": "dp%d DDP/NCCL" % world,
+                          "l2": "flushed between timed iterations (256 MiB write outside the event pairs)"},
+               "clocks": clocks,
+               "e2e": {"value": round(total / (ms_e2e / 1e3), 1), "unit": "examples/s",
+                       "ms_per_step": round(ms_e2e / args.steps, 4),
+                       "h2d_bytes_per_step": sum(v.numel() * 4 for v in batches[0].values()),
+                       "d2h_bytes_per_step": 4},
+               "gpu_launches": 0}
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    return res
