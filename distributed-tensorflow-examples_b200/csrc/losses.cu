@@ -154,24 +154,25 @@ __global__ void __launch_bounds__(1024) softmax_xent_grad_kernel(const float* __
                                                                  int B, int C, float* loss, __nv_bfloat16* dz,
                                                                  int ld_dz, __nv_bfloat16* dz_t, int ld_dzt,
                                                                  float* colsum, float* correct) {
-    __shared__ float s_loss, s_corr;
-    __shared__ float s_col[32];
-    if (threadIdx.x == 0) { s_loss = 0.0f; s_corr = 0.0f; }
-    if (threadIdx.x < 32) s_col[threadIdx.x] = 0.0f;
-    __syncthreads();
+    __shared__ float s_part[32][34];     // [warp][0..31 column sums, 32 loss, 33 correct]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const float invB = 1.0f / static_cast<float>(B);
+    float col[32];
+#pragma unroll
+    for (int c = 0; c < 32; ++c) col[c] = 0.0f;
+    float l_acc = 0.0f, corr = 0.0f;
     for (int r = threadIdx.x; r < B; r += blockDim.x) {
-        float z[32];
+        float z[32], y[32];
         float mx = -INFINITY, ysum = 0.0f, ymax = -INFINITY;
         int am = 0, ay = 0;
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
             if (c < C) {
                 z[c] = logits[static_cast<size_t>(r) * ld + c];
-                const float yv = labels[static_cast<size_t>(r) * ld_l + c];
+                y[c] = labels[static_cast<size_t>(r) * ld_l + c];
                 if (z[c] > mx) { mx = z[c]; am = c; }
-                if (yv > ymax) { ymax = yv; ay = c; }
-                ysum += yv;
+                if (y[c] > ymax) { ymax = y[c]; ay = c; }
+                ysum += y[c];
             }
         }
         float se = 0.0f;
@@ -179,29 +180,43 @@ __global__ void __launch_bounds__(1024) softmax_xent_grad_kernel(const float* __
         for (int c = 0; c < 32; ++c)
             if (c < C) se += __expf(z[c] - mx);
         const float lse = mx + __logf(se);
-        float l = 0.0f;
 #pragma unroll
         for (int c = 0; c < 32; ++c) {
             if (c < C) {
-                const float yv = labels[static_cast<size_t>(r) * ld_l + c];
-                l -= yv * (z[c] - lse);
-                const float g = (__expf(z[c] - lse) * ysum - yv) * invB;
+                l_acc -= y[c] * (z[c] - lse);
+                const float g = (__expf(z[c] - lse) * ysum - y[c]) * invB;
+                col[c] += g;
                 if (dz != nullptr) dz[static_cast<size_t>(r) * ld_dz + c] = __float2bfloat16_rn(g);
                 if (dz_t != nullptr) dz_t[static_cast<size_t>(c) * ld_dzt + r] = __float2bfloat16_rn(g);
-                if (colsum != nullptr) atomicAdd(&s_col[c], g);
             }
         }
         if (dz != nullptr)
             for (int c = C; c < ld_dz && c < ((C + 7) & ~7); ++c) dz[static_cast<size_t>(r) * ld_dz + c] = __float2bfloat16_rn(0.0f);
-        atomicAdd(&s_loss, l);
-        if (am == ay) atomicAdd(&s_corr, 1.0f);
+        if (am == ay) corr += 1.0f;
     }
+    // warp reductions, then one pass over the per-warp partials
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+        if (c < C) {
+            const float s = warp_sum(col[c]);
+            if (lane == 0) s_part[warp][c] = s;
+        }
+    }
+    l_acc = warp_sum(l_acc);
+    corr = warp_sum(corr);
+    if (lane == 0) { s_part[warp][32] = l_acc; s_part[warp][33] = corr; }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        *loss = s_loss * invB;
-        if (correct != nullptr) *correct = s_corr;
+    if (warp == 0) {
+        for (int k = lane; k < 34; k += 32) {
+            if (k < C || k >= 32) {
+                float s = 0.0f;
+                for (int w = 0; w < nwarps; ++w) s += s_part[w][k];
+                if (k < C) { if (colsum != nullptr) atomicAdd(colsum + k, s); }
+                else if (k == 32) *loss = s * invB;
+                else if (correct != nullptr) *correct = s;
+            }
+        }
     }
-    if (colsum != nullptr && threadIdx.x < C) atomicAdd(colsum + threadIdx.x, s_col[threadIdx.x]);
 }
 
 }  // namespace psb

@@ -6,16 +6,20 @@
 //       A = Wt (the cell kernel transposed, bf16, resident in shared memory for the whole
 //           sequence), B = [x_t, h_{t-1}] of this CTA's 16 batch rows, D in TMEM:
 //           gate g occupies TMEM columns [16g, 16g+16), lane = hidden unit.
-//       The 128 epilogue threads (thread = hidden unit) read i,j,f,o for their unit and 16
-//       batch rows, do the sigmoid/tanh pointwise with c held in registers, and write h_t
-//       straight back into the B-operand tile in shared memory for the next step.
+//       256 pointwise threads (thread = hidden unit x half of the batch slice) read i,j,f,o
+//       for their unit from TMEM, do the sigmoid/tanh math with c held in registers, and
+//       write h_t straight back into the B-operand tile in shared memory for the next step.
 //   backward, per timestep:  dh_{t-1}^T[H, nb] = Wh[H, 4H] * dG_t^T[4H, nb]
 //       A = rows I.. of the kernel in its natural layout, B = the gate gradients the same
-//       threads just produced.
+//       threads just produced; the saved activations of step t-1 are prefetched while the
+//       MMA of step t is in flight.
 //
 // One CTA per 16 batch rows, no inter-CTA synchronisation; the sequence loop never leaves
-// the SM.  The weight load at kernel start uses plain 16-byte global loads, so the weight
-// pointer may be a peer GPU's HBM (parameter pull fused into the consuming kernel).
+// the SM.  The weight load at kernel start is cp.async from plain global addresses, so the
+// weight pointer may be a peer GPU's HBM (parameter pull fused into the consuming kernel).
+//
+// Saved-for-backward blobs (private layout shared by the two kernels, 16-byte vectors per
+// thread):   gates[t][cta][u][g][16] bf16 (activated i,j,f,o)     c[t][cta][u][16] fp32
 //
 // ref: rnn.BasicLSTMCell(num_hidden, forget_bias=1.0) + rnn.static_rnn, lstm:50-52, and the
 //      backward that optimizer.minimize builds for it, lstm:97.
@@ -27,7 +31,9 @@ namespace psb {
 
 constexpr int kH = 128;              // hidden units (UMMA M of one gate block)
 constexpr int kNB = 16;              // batch rows per CTA (UMMA N)
-constexpr int kLstmThreads = 160;    // 4 epilogue warps + 1 MMA warp
+constexpr int kHB = 8;               // batch rows per pointwise thread
+constexpr int kPW = 256;             // pointwise threads (8 warps)
+constexpr int kLstmThreads = kPW + 32;   // + 1 MMA warp
 constexpr int kFwdKB = 3;            // k-blocks of 64 covering I+H <= 192
 constexpr int kFwdASmem = kFwdKB * 4 * kH * 128;   // 196608
 constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144
@@ -44,6 +50,10 @@ __device__ __forceinline__ uint32_t swz_off(int rows, int row, int k) {
     return static_cast<uint32_t>(kb * rows * 128 + row * 128 + ((((kk >> 3) ^ (row & 7)) << 4)) + ((kk & 7) << 1));
 }
 
+__device__ __forceinline__ void sts_bf16(uint8_t* base, uint32_t off, uint32_t packed_lo16) {
+    *reinterpret_cast<uint16_t*>(base + off) = static_cast<uint16_t>(packed_lo16);
+}
+
 struct LstmFwdArgs {
     const float* x;              // [B, T, I] fp32
     const __nv_bfloat16* wt;     // [4H, ld_wt] bf16 = kernel^T (may be peer memory)
@@ -56,8 +66,8 @@ struct LstmFwdArgs {
     __nv_bfloat16* h_last_t;     // [H, ld_ht] bf16 (nullable)
     int ld_ht;
     // saved for backward (all nullable together)
-    __nv_bfloat16* gates;        // [T, 4, B, H] bf16, activated i, j, f, o
-    float* c_all;                // [T, B, H] fp32, c after step t
+    uint4* gates;                // blob, see header comment
+    float4* c_all;               // blob
     __nv_bfloat16* xh_t;         // [I+H, ld_xht] bf16: row k, column t*B + b = xh_t[b, k]
     int ld_xht;
 };
@@ -75,45 +85,45 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
     const int K = a.I + kH;
 
     if (tid == 0) {
-        mbar_init(&xh_ready, 128);
+        mbar_init(&xh_ready, kPW);
         mbar_init(&mma_done, 1);
         fence_mbar_init();
     }
-    if (warp == 4) tmem_alloc<64>(&tmem_slot);
+    if (warp == 8) tmem_alloc<64>(&tmem_slot);
 
-    // ---- weights: global (possibly peer) -> swizzled shared, 16 bytes at a time
+    // ---- weights: global (possibly peer) -> swizzled shared, 16 bytes per cp.async
     {
         const int chunks_per_row = kFwdKB * 8;                 // 24 chunks of 8 bf16
         const int total = 4 * kH * chunks_per_row;
         for (int idx = tid; idx < total; idx += kLstmThreads) {
             const int r = idx / chunks_per_row, c = idx % chunks_per_row;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (c * 8 < a.ld_wt) v = *reinterpret_cast<const uint4*>(a.wt + static_cast<size_t>(r) * a.ld_wt + c * 8);
-            *reinterpret_cast<uint4*>(sA + swz_off(4 * kH, r, c * 8)) = v;
+            uint8_t* dst = sA + swz_off(4 * kH, r, c * 8);
+            if (c * 8 < a.ld_wt) cp_async_16(dst, a.wt + static_cast<size_t>(r) * a.ld_wt + c * 8);
+            else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
         }
         for (int idx = tid; idx < kFwdBSmem / 16; idx += kLstmThreads)
             reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
     }
     __syncthreads();   // sB zeroed before x_0 goes in
 
-    const int x_per_step = kNB * a.I;      // elements of x this CTA consumes per step
-    if (warp < 4) {
-        for (int e = tid; e < x_per_step; e += 128) {
+    const int x_per_step = kNB * a.I;      // <= 512 elements of x per step for this CTA
+    if (warp < 8) {
+        for (int e = tid; e < x_per_step; e += kPW) {
             const int b = e / a.I, i = e % a.I;
-            float xv = (b0 + b < a.B) ? a.x[(static_cast<size_t>(b0 + b) * a.T + 0) * a.I + i] : 0.0f;
-            __nv_bfloat16 xb = __float2bfloat16_rn(xv);
+            const float xv = (b0 + b < a.B) ? a.x[(static_cast<size_t>(b0 + b) * a.T + 0) * a.I + i] : 0.0f;
+            const __nv_bfloat16 xb = __float2bfloat16_rn(xv);
             *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, i)) = xb;
-            if (a.xh_t != nullptr && b0 + b < a.B)
-                a.xh_t[static_cast<size_t>(i) * a.ld_xht + 0 * a.B + b0 + b] = xb;
+            if (a.xh_t != nullptr && b0 + b < a.B) a.xh_t[static_cast<size_t>(i) * a.ld_xht + b0 + b] = xb;
         }
     }
+    cp_async_wait_all();
     fence_proxy_async_smem();
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem = tmem_slot;
 
-    if (warp == 4) {
+    if (warp == 8) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
@@ -137,22 +147,26 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
             }
         }
     } else {
-        // ===================== pointwise / state threads (thread = hidden unit) =====================
-        const int u = static_cast<int>(tid);
-        const uint32_t t_lane = tmem + ((warp * 32u) << 16);
+        // ===================== pointwise / state threads =====================
+        const int u = static_cast<int>(tid & 127);          // hidden unit == TMEM lane
+        const int half = static_cast<int>(tid >> 7);        // which 8 batch rows of the slice
+        const int bb = half * kHB;
+        const uint32_t t_lane = tmem + (((warp & 3u) * 32u) << 16) + bb;
         const float bi = a.bias[u], bj = a.bias[kH + u], bf = a.bias[2 * kH + u] + a.forget_bias,
                     bo = a.bias[3 * kH + u];
-        float c[kNB];
+        const bool full = (b0 + kNB <= a.B);
+        const size_t blob_row = static_cast<size_t>(gridDim.x) * kH;     // (cta,u) rows per timestep
+        float c[kHB];
 #pragma unroll
-        for (int b = 0; b < kNB; ++b) c[b] = 0.0f;
+        for (int b = 0; b < kHB; ++b) c[b] = 0.0f;
 
         for (int t = 0; t < a.T; ++t) {
             // prefetch x_{t+1} for this slice (independent of the recurrence)
-            float xn[4];
+            float xn[2];
             const bool more = t + 1 < a.T;
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int e = u + q * 128;
+            for (int q = 0; q < 2; ++q) {
+                const int e = static_cast<int>(tid) + q * kPW;
                 xn[q] = 0.0f;
                 if (more && e < x_per_step) {
                     const int b = e / a.I, i = e % a.I;
@@ -161,70 +175,90 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
             }
             mbar_wait(&mma_done, t & 1);
             tc_fence_after_sync();
-            uint32_t ri[16], rj[16], rf[16], ro[16];
-            tmem_ld_32x16(t_lane + 0 * kNB, ri);
-            tmem_ld_32x16(t_lane + 1 * kNB, rj);
-            tmem_ld_32x16(t_lane + 2 * kNB, rf);
-            tmem_ld_32x16(t_lane + 3 * kNB, ro);
+            uint32_t ri[8], rj[8], rf[8], ro[8];
+            tmem_ld_32x8(t_lane + 0 * kNB, ri);
+            tmem_ld_32x8(t_lane + 1 * kNB, rj);
+            tmem_ld_32x8(t_lane + 2 * kNB, rf);
+            tmem_ld_32x8(t_lane + 3 * kNB, ro);
             tmem_ld_wait();
 
-            __align__(16) __nv_bfloat16 hb[kNB];
+            float ig[kHB], jg[kHB], fg[kHB], og[kHB], h[kHB];
 #pragma unroll
-            for (int b = 0; b < kNB; ++b) {
-                const float ig = sigmoid_t(__uint_as_float(ri[b]) + bi);
-                const float jg = fast_tanh(__uint_as_float(rj[b]) + bj);
-                const float fg = sigmoid_t(__uint_as_float(rf[b]) + bf);
-                const float og = sigmoid_t(__uint_as_float(ro[b]) + bo);
-                c[b] = fmaf(c[b], fg, ig * jg);
-                const float h = fast_tanh(c[b]) * og;
-                hb[b] = __float2bfloat16_rn(h);
-                if (a.gates != nullptr && b0 + b < a.B) {
-                    const size_t base = (static_cast<size_t>(t) * 4 * a.B + (b0 + b)) * kH + u;
-                    const size_t gs = static_cast<size_t>(a.B) * kH;
-                    a.gates[base] = __float2bfloat16_rn(ig);
-                    a.gates[base + gs] = __float2bfloat16_rn(jg);
-                    a.gates[base + 2 * gs] = __float2bfloat16_rn(fg);
-                    a.gates[base + 3 * gs] = __float2bfloat16_rn(og);
-                    a.c_all[(static_cast<size_t>(t) * a.B + (b0 + b)) * kH + u] = c[b];
-                }
+            for (int b = 0; b < kHB; ++b) {
+                ig[b] = sigmoid_t(__uint_as_float(ri[b]) + bi);
+                jg[b] = fast_tanh(__uint_as_float(rj[b]) + bj);
+                fg[b] = sigmoid_t(__uint_as_float(rf[b]) + bf);
+                og[b] = sigmoid_t(__uint_as_float(ro[b]) + bo);
+                c[b] = fmaf(c[b], fg[b], ig[b] * jg[b]);
+                h[b] = fast_tanh(c[b]) * og[b];
             }
+            uint4 hp;
+            hp.x = pack_bf16(h[0], h[1]); hp.y = pack_bf16(h[2], h[3]);
+            hp.z = pack_bf16(h[4], h[5]); hp.w = pack_bf16(h[6], h[7]);
             if (more) {
-                // h_t -> B operand (columns I..I+H) and x_{t+1} -> columns 0..I
+                // h_t -> B operand (columns I..I+H), rows bb..bb+7
+                const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
 #pragma unroll
-                for (int b = 0; b < kNB; ++b)
-                    *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, a.I + u)) = hb[b];
+                for (int p = 0; p < 4; ++p) {
+                    sts_bf16(sB, swz_off(kNB, bb + 2 * p, a.I + u), hv[p] & 0xffffu);
+                    sts_bf16(sB, swz_off(kNB, bb + 2 * p + 1, a.I + u), hv[p] >> 16);
+                }
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int e = u + q * 128;
+                for (int q = 0; q < 2; ++q) {
+                    const int e = static_cast<int>(tid) + q * kPW;
                     if (e < x_per_step) {
                         const int b = e / a.I, i = e % a.I;
-                        __nv_bfloat16 xb = __float2bfloat16_rn(xn[q]);
+                        const __nv_bfloat16 xb = __float2bfloat16_rn(xn[q]);
                         *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, i)) = xb;
                         if (a.xh_t != nullptr && b0 + b < a.B)
                             a.xh_t[static_cast<size_t>(i) * a.ld_xht + static_cast<size_t>(t + 1) * a.B + b0 + b] = xb;
                     }
                 }
-                if (a.xh_t != nullptr) {
-                    // h_t is the recurrent input of step t+1: row I+u, columns (t+1)*B + b0 ..
-                    __nv_bfloat16* dst = a.xh_t + static_cast<size_t>(a.I + u) * a.ld_xht +
-                                         static_cast<size_t>(t + 1) * a.B + b0;
-                    if (b0 + kNB <= a.B) {
-                        const uint4* src = reinterpret_cast<const uint4*>(hb);
-                        reinterpret_cast<uint4*>(dst)[0] = src[0];
-                        reinterpret_cast<uint4*>(dst)[1] = src[1];
-                    } else {
-                        for (int b = 0; b < kNB && b0 + b < a.B; ++b) dst[b] = hb[b];
-                    }
-                }
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
                 mbar_arrive(&xh_ready);
-            } else {
+            }
+            // ---- everything below is off the recurrence's critical path
+            if (a.gates != nullptr) {
+                const size_t row = static_cast<size_t>(t) * blob_row + static_cast<size_t>(blockIdx.x) * kH + u;
+                uint4* gp = a.gates + row * 8 + half;            // 8 uint4 per (t,cta,u): [g][2 halves]
+                uint4 v;
+                v.x = pack_bf16(ig[0], ig[1]); v.y = pack_bf16(ig[2], ig[3]); v.z = pack_bf16(ig[4], ig[5]); v.w = pack_bf16(ig[6], ig[7]);
+                gp[0] = v;
+                v.x = pack_bf16(jg[0], jg[1]); v.y = pack_bf16(jg[2], jg[3]); v.z = pack_bf16(jg[4], jg[5]); v.w = pack_bf16(jg[6], jg[7]);
+                gp[2] = v;
+                v.x = pack_bf16(fg[0], fg[1]); v.y = pack_bf16(fg[2], fg[3]); v.z = pack_bf16(fg[4], fg[5]); v.w = pack_bf16(fg[6], fg[7]);
+                gp[4] = v;
+                v.x = pack_bf16(og[0], og[1]); v.y = pack_bf16(og[2], og[3]); v.z = pack_bf16(og[4], og[5]); v.w = pack_bf16(og[6], og[7]);
+                gp[6] = v;
+                float4* cp = a.c_all + row * 4 + half * 2;       // 4 float4 per (t,cta,u)
+                cp[0] = make_float4(c[0], c[1], c[2], c[3]);
+                cp[1] = make_float4(c[4], c[5], c[6], c[7]);
+                if (more) {
+                    // h_t is the recurrent input of step t+1: row I+u, columns (t+1)*B + b0 + bb ..
+                    __nv_bfloat16* dst = a.xh_t + static_cast<size_t>(a.I + u) * a.ld_xht +
+                                         static_cast<size_t>(t + 1) * a.B + b0 + bb;
+                    if (full) {
+                        *reinterpret_cast<uint4*>(dst) = hp;
+                    } else {
+                        const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
+                        for (int b = 0; b < kHB && b0 + bb + b < a.B; ++b) {
+                            const uint16_t bits = static_cast<uint16_t>((b & 1) ? (hv[b >> 1] >> 16) : (hv[b >> 1] & 0xffffu));
+                            *reinterpret_cast<uint16_t*>(dst + b) = bits;
+                        }
+                    }
+                }
+            }
+            if (!more) {
+                const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
 #pragma unroll
-                for (int b = 0; b < kNB; ++b) {
-                    if (b0 + b < a.B) {
-                        if (a.h_last != nullptr) a.h_last[static_cast<size_t>(b0 + b) * a.ld_h + u] = hb[b];
-                        if (a.h_last_t != nullptr) a.h_last_t[static_cast<size_t>(u) * a.ld_ht + b0 + b] = hb[b];
+                for (int b = 0; b < kHB; ++b) {
+                    if (b0 + bb + b < a.B) {
+                        const uint16_t bits = static_cast<uint16_t>((b & 1) ? (hv[b >> 1] >> 16) : (hv[b >> 1] & 0xffffu));
+                        if (a.h_last != nullptr)
+                            *reinterpret_cast<uint16_t*>(a.h_last + static_cast<size_t>(b0 + bb + b) * a.ld_h + u) = bits;
+                        if (a.h_last_t != nullptr)
+                            *reinterpret_cast<uint16_t*>(a.h_last_t + static_cast<size_t>(u) * a.ld_ht + b0 + bb + b) = bits;
                     }
                 }
                 tc_fence_before_sync();
@@ -232,7 +266,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
         }
     }
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 8) {
         tc_fence_after_sync();
         tmem_dealloc<64>(tmem);
     }
@@ -243,8 +277,8 @@ struct LstmBwdArgs {
     int ld_w;
     const float* dh_last;        // [B, ld_dh] fp32
     int ld_dh;
-    const __nv_bfloat16* gates;  // [T, 4, B, H]
-    const float* c_all;          // [T, B, H]
+    const uint4* gates;          // blob written by lstm_fwd_kernel
+    const float4* c_all;         // blob
     int B, T, I;
     __nv_bfloat16* dg_t;         // [4H, ld_dgt] bf16: row g*H+u, column t*B + b
     int ld_dgt;
@@ -263,27 +297,27 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     const int b0 = blockIdx.x * kNB;
 
     if (tid == 0) {
-        mbar_init(&dg_ready, 128);
+        mbar_init(&dg_ready, kPW);
         mbar_init(&mma_done, 1);
         fence_mbar_init();
     }
-    if (warp == 4) tmem_alloc<32>(&tmem_slot);
+    if (warp == 8) tmem_alloc<32>(&tmem_slot);
     {
         // Wh = kernel rows I..I+H, each 4H = 512 bf16 = 64 chunks of 16 bytes
         const int total = kH * 64;
         for (int idx = tid; idx < total; idx += kLstmThreads) {
             const int r = idx >> 6, c = idx & 63;
-            uint4 v = *reinterpret_cast<const uint4*>(a.w + static_cast<size_t>(a.I + r) * a.ld_w + c * 8);
-            *reinterpret_cast<uint4*>(sA + swz_off(kH, r, c * 8)) = v;
+            cp_async_16(sA + swz_off(kH, r, c * 8), a.w + static_cast<size_t>(a.I + r) * a.ld_w + c * 8);
         }
     }
+    cp_async_wait_all();
     fence_proxy_async_smem();
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem = tmem_slot;
 
-    if (warp == 4) {
+    if (warp == 8) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
             const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
@@ -301,78 +335,119 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
             }
         }
     } else {
-        const int u = static_cast<int>(tid);
-        const uint32_t t_lane = tmem + ((warp * 32u) << 16);
-        float dh[kNB], dc[kNB];
+        const int u = static_cast<int>(tid & 127);
+        const int half = static_cast<int>(tid >> 7);
+        const int bb = half * kHB;
+        const uint32_t t_lane = tmem + (((warp & 3u) * 32u) << 16) + bb;
+        const bool full = (b0 + kNB <= a.B);
+        const size_t blob_row = static_cast<size_t>(gridDim.x) * kH;
+        float dh[kHB], dc[kHB], c_new[kHB], c_old[kHB];
         float dbs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int b = 0; b < kNB; ++b) {
-            dh[b] = (b0 + b < a.B) ? a.dh_last[static_cast<size_t>(b0 + b) * a.ld_dh + u] : 0.0f;
+        for (int b = 0; b < kHB; ++b) {
+            dh[b] = (b0 + bb + b < a.B) ? a.dh_last[static_cast<size_t>(b0 + bb + b) * a.ld_dh + u] : 0.0f;
             dc[b] = 0.0f;
         }
-        const size_t gs = static_cast<size_t>(a.B) * kH;
+        // saved activations of the last step
+        uint4 gq[4];
+        {
+            const size_t row = static_cast<size_t>(a.T - 1) * blob_row + static_cast<size_t>(blockIdx.x) * kH + u;
+#pragma unroll
+            for (int g = 0; g < 4; ++g) gq[g] = a.gates[row * 8 + 2 * g + half];
+            const float4 c0 = a.c_all[row * 4 + half * 2], c1 = a.c_all[row * 4 + half * 2 + 1];
+            c_new[0] = c0.x; c_new[1] = c0.y; c_new[2] = c0.z; c_new[3] = c0.w;
+            c_new[4] = c1.x; c_new[5] = c1.y; c_new[6] = c1.z; c_new[7] = c1.w;
+            if (a.T > 1) {
+                const size_t rowp = row - blob_row;
+                const float4 p0 = a.c_all[rowp * 4 + half * 2], p1 = a.c_all[rowp * 4 + half * 2 + 1];
+                c_old[0] = p0.x; c_old[1] = p0.y; c_old[2] = p0.z; c_old[3] = p0.w;
+                c_old[4] = p1.x; c_old[5] = p1.y; c_old[6] = p1.z; c_old[7] = p1.w;
+            } else {
+#pragma unroll
+                for (int b = 0; b < kHB; ++b) c_old[b] = 0.0f;
+            }
+        }
         for (int t = a.T - 1, s = 0; t >= 0; --t, ++s) {
-            __align__(16) __nv_bfloat16 dgi[kNB], dgj[kNB], dgf[kNB], dgo[kNB];
+            float di[kHB], dj[kHB], df[kHB], dO[kHB];
+            const uint32_t gi[4] = {gq[0].x, gq[0].y, gq[0].z, gq[0].w};
+            const uint32_t gj[4] = {gq[1].x, gq[1].y, gq[1].z, gq[1].w};
+            const uint32_t gf[4] = {gq[2].x, gq[2].y, gq[2].z, gq[2].w};
+            const uint32_t go[4] = {gq[3].x, gq[3].y, gq[3].z, gq[3].w};
 #pragma unroll
-            for (int b = 0; b < kNB; ++b) {
-                float di = 0.f, dj = 0.f, df = 0.f, dO = 0.f;
-                if (b0 + b < a.B) {
-                    const size_t base = (static_cast<size_t>(t) * 4 * a.B + (b0 + b)) * kH + u;
-                    const float ig = __bfloat162float(a.gates[base]);
-                    const float jg = __bfloat162float(a.gates[base + gs]);
-                    const float fg = __bfloat162float(a.gates[base + 2 * gs]);
-                    const float og = __bfloat162float(a.gates[base + 3 * gs]);
-                    const float cn = a.c_all[(static_cast<size_t>(t) * a.B + (b0 + b)) * kH + u];
-                    const float co = (t > 0) ? a.c_all[(static_cast<size_t>(t - 1) * a.B + (b0 + b)) * kH + u] : 0.0f;
-                    const float tc = fast_tanh(cn);
-                    const float dcv = fmaf(dh[b] * og, 1.0f - tc * tc, dc[b]);
-                    dO = dh[b] * tc * og * (1.0f - og);
-                    di = dcv * jg * ig * (1.0f - ig);
-                    dj = dcv * ig * (1.0f - jg * jg);
-                    df = dcv * co * fg * (1.0f - fg);
-                    dc[b] = dcv * fg;
-                }
-                dbs[0] += di; dbs[1] += dj; dbs[2] += df; dbs[3] += dO;
-                dgi[b] = __float2bfloat16_rn(di);
-                dgj[b] = __float2bfloat16_rn(dj);
-                dgf[b] = __float2bfloat16_rn(df);
-                dgo[b] = __float2bfloat16_rn(dO);
+            for (int b = 0; b < kHB; ++b) {
+                const float ig = (b & 1) ? bf16_hi(gi[b >> 1]) : bf16_lo(gi[b >> 1]);
+                const float jg = (b & 1) ? bf16_hi(gj[b >> 1]) : bf16_lo(gj[b >> 1]);
+                const float fg = (b & 1) ? bf16_hi(gf[b >> 1]) : bf16_lo(gf[b >> 1]);
+                const float og = (b & 1) ? bf16_hi(go[b >> 1]) : bf16_lo(go[b >> 1]);
+                const float tc = fast_tanh(c_new[b]);
+                const float dcv = fmaf(dh[b] * og, 1.0f - tc * tc, dc[b]);
+                dO[b] = dh[b] * tc * og * (1.0f - og);
+                di[b] = dcv * jg * ig * (1.0f - ig);
+                dj[b] = dcv * ig * (1.0f - jg * jg);
+                df[b] = dcv * c_old[b] * fg * (1.0f - fg);
+                dc[b] = dcv * fg;
+                dbs[0] += di[b]; dbs[1] += dj[b]; dbs[2] += df[b]; dbs[3] += dO[b];
             }
-            // gate gradients for the weight-gradient GEMM: row g*H+u, 16 consecutive columns
-            if (a.dg_t != nullptr) {
-                const __nv_bfloat16* srcs[4] = {dgi, dgj, dgf, dgo};
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    __nv_bfloat16* dst = a.dg_t + static_cast<size_t>(g * kH + u) * a.ld_dgt +
-                                         static_cast<size_t>(t) * a.B + b0;
-                    if (b0 + kNB <= a.B) {
-                        const uint4* src = reinterpret_cast<const uint4*>(srcs[g]);
-                        reinterpret_cast<uint4*>(dst)[0] = src[0];
-                        reinterpret_cast<uint4*>(dst)[1] = src[1];
-                    } else {
-                        for (int b = 0; b < kNB && b0 + b < a.B; ++b) dst[b] = srcs[g][b];
-                    }
-                }
-            }
+            uint4 pk[4];
+            pk[0].x = pack_bf16(di[0], di[1]); pk[0].y = pack_bf16(di[2], di[3]); pk[0].z = pack_bf16(di[4], di[5]); pk[0].w = pack_bf16(di[6], di[7]);
+            pk[1].x = pack_bf16(dj[0], dj[1]); pk[1].y = pack_bf16(dj[2], dj[3]); pk[1].z = pack_bf16(dj[4], dj[5]); pk[1].w = pack_bf16(dj[6], dj[7]);
+            pk[2].x = pack_bf16(df[0], df[1]); pk[2].y = pack_bf16(df[2], df[3]); pk[2].z = pack_bf16(df[4], df[5]); pk[2].w = pack_bf16(df[6], df[7]);
+            pk[3].x = pack_bf16(dO[0], dO[1]); pk[3].y = pack_bf16(dO[2], dO[3]); pk[3].z = pack_bf16(dO[4], dO[5]); pk[3].w = pack_bf16(dO[6], dO[7]);
             if (t > 0) {
                 // B operand of dh_{t-1}^T = Wh * dG_t^T : element (row b, col g*H+u)
 #pragma unroll
-                for (int b = 0; b < kNB; ++b) {
-                    *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, 0 * kH + u)) = dgi[b];
-                    *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, 1 * kH + u)) = dgj[b];
-                    *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, 2 * kH + u)) = dgf[b];
-                    *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, 3 * kH + u)) = dgo[b];
+                for (int g = 0; g < 4; ++g) {
+                    const uint32_t v[4] = {pk[g].x, pk[g].y, pk[g].z, pk[g].w};
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) {
+                        sts_bf16(sB, swz_off(kNB, bb + 2 * p, g * kH + u), v[p] & 0xffffu);
+                        sts_bf16(sB, swz_off(kNB, bb + 2 * p + 1, g * kH + u), v[p] >> 16);
+                    }
                 }
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
                 mbar_arrive(&dg_ready);
+            }
+            // gate gradients for the weight-gradient GEMM: row g*H+u, 8 consecutive columns
+            if (a.dg_t != nullptr) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) {
+                    __nv_bfloat16* dst = a.dg_t + static_cast<size_t>(g * kH + u) * a.ld_dgt +
+                                         static_cast<size_t>(t) * a.B + b0 + bb;
+                    if (full) {
+                        *reinterpret_cast<uint4*>(dst) = pk[g];
+                    } else {
+                        const uint32_t v[4] = {pk[g].x, pk[g].y, pk[g].z, pk[g].w};
+                        for (int b = 0; b < kHB && b0 + bb + b < a.B; ++b) {
+                            const uint16_t bits = static_cast<uint16_t>((b & 1) ? (v[b >> 1] >> 16) : (v[b >> 1] & 0xffffu));
+                            *reinterpret_cast<uint16_t*>(dst + b) = bits;
+                        }
+                    }
+                }
+            }
+            if (t > 0) {
+                // prefetch the saved activations of step t-1 while the MMA runs
+                const size_t row = static_cast<size_t>(t - 1) * blob_row + static_cast<size_t>(blockIdx.x) * kH + u;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) gq[g] = a.gates[row * 8 + 2 * g + half];
+#pragma unroll
+                for (int b = 0; b < kHB; ++b) c_new[b] = c_old[b];
+                if (t > 1) {
+                    const size_t rowp = row - blob_row;
+                    const float4 p0 = a.c_all[rowp * 4 + half * 2], p1 = a.c_all[rowp * 4 + half * 2 + 1];
+                    c_old[0] = p0.x; c_old[1] = p0.y; c_old[2] = p0.z; c_old[3] = p0.w;
+                    c_old[4] = p1.x; c_old[5] = p1.y; c_old[6] = p1.z; c_old[7] = p1.w;
+                } else {
+#pragma unroll
+                    for (int b = 0; b < kHB; ++b) c_old[b] = 0.0f;
+                }
                 mbar_wait(&mma_done, s & 1);
                 tc_fence_after_sync();
-                uint32_t r[16];
-                tmem_ld_32x16(t_lane, r);
+                uint32_t r[8];
+                tmem_ld_32x8(t_lane, r);
                 tmem_ld_wait();
 #pragma unroll
-                for (int b = 0; b < kNB; ++b) dh[b] = __uint_as_float(r[b]);
+                for (int b = 0; b < kHB; ++b) dh[b] = __uint_as_float(r[b]);
             }
         }
         if (a.dbias != nullptr) {
@@ -382,13 +457,20 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         tc_fence_before_sync();
     }
     __syncthreads();
-    if (warp == 4) {
+    if (warp == 8) {
         tc_fence_after_sync();
         tmem_dealloc<32>(tmem);
     }
 }
 
 }  // namespace psb
+
+extern "C" size_t psb_lstm_saved_bytes(int B, int T, int H, int which) {
+    // which: 0 = gates blob, 1 = c blob
+    const size_t ctas = (static_cast<size_t>(B) + psb::kNB - 1) / psb::kNB;
+    const size_t rows = static_cast<size_t>(T) * ctas * static_cast<size_t>(H);
+    return which == 0 ? rows * 8 * 16 : rows * 4 * 16;
+}
 
 extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const float* bias,
                             float forget_bias, int B, int T, int I, int H, void* h_last, int ld_h,
@@ -402,12 +484,14 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
     if ((gates != nullptr) != (c_all != nullptr) || (gates != nullptr) != (xh_t != nullptr))
         return fail(PSB_ERR_ARG, "psb_lstm_fwd: gates, c_all and xh_t must be given together");
     if (xh_t && (ld_xht % 8 || B % 8)) return fail(PSB_ERR_ARG, "psb_lstm_fwd: saving needs B%%8==0 and ld_xht%%8==0");
+    if (gates && ((reinterpret_cast<uintptr_t>(gates) | reinterpret_cast<uintptr_t>(c_all)) & 15))
+        return fail(PSB_ERR_ARG, "psb_lstm_fwd: gates and c_all must be 16-byte aligned");
     LstmFwdArgs a;
     a.x = x; a.wt = static_cast<const __nv_bfloat16*>(wt); a.ld_wt = ld_wt; a.bias = bias;
     a.forget_bias = forget_bias; a.B = B; a.T = T; a.I = I;
     a.h_last = static_cast<__nv_bfloat16*>(h_last); a.ld_h = ld_h;
     a.h_last_t = static_cast<__nv_bfloat16*>(h_last_t); a.ld_ht = ld_ht;
-    a.gates = static_cast<__nv_bfloat16*>(gates); a.c_all = c_all;
+    a.gates = static_cast<uint4*>(gates); a.c_all = reinterpret_cast<float4*>(c_all);
     a.xh_t = static_cast<__nv_bfloat16*>(xh_t); a.ld_xht = ld_xht;
     const size_t smem = kFwdASmem + kFwdBSmem + 1024;
     static bool attr = false;
@@ -429,7 +513,8 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     if (dg_t && (ld_dgt % 8 || B % 8)) return fail(PSB_ERR_ARG, "psb_lstm_bwd: dg_t needs B%%8==0 and ld_dgt%%8==0");
     LstmBwdArgs a;
     a.w = static_cast<const __nv_bfloat16*>(w); a.ld_w = ld_w; a.dh_last = dh_last; a.ld_dh = ld_dh;
-    a.gates = static_cast<const __nv_bfloat16*>(gates); a.c_all = c_all; a.B = B; a.T = T; a.I = I;
+    a.gates = static_cast<const uint4*>(gates); a.c_all = reinterpret_cast<const float4*>(c_all);
+    a.B = B; a.T = T; a.I = I;
     a.dg_t = static_cast<__nv_bfloat16*>(dg_t); a.ld_dgt = ld_dgt; a.dbias = dbias;
     const size_t smem = kBwdASmem + kBwdBSmem + 1024;
     static bool attr = false;

@@ -139,10 +139,25 @@ class LstmSaved:
 
     def __init__(self, B: int, T: int, I: int, H: int, device="cuda"):
         self.B, self.T, self.I, self.H = B, T, I, H
-        self.gates = torch.zeros(T, 4, B, H, dtype=torch.bfloat16, device=device)
-        self.c_all = torch.zeros(T, B, H, dtype=torch.float32, device=device)
+        L = _lib.lib()
+        L.psb_lstm_saved_bytes.restype = ctypes.c_size_t
+        L.psb_lstm_saved_bytes.argtypes = [c_int, c_int, c_int, c_int]
+        self.ctas = (B + 15) // 16
+        # opaque blobs in the kernels' private layout: [t][cta][unit][gate][16] / [t][cta][unit][16]
+        self.gates = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 0) // 2, dtype=torch.bfloat16, device=device)
+        self.c_all = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 1) // 4, dtype=torch.float32, device=device)
         self.xh_t = BMat(I + H, T * B, device)       # [I+H, T*B]
         self.dg_t = BMat(4 * H, T * B, device)       # [4H, T*B]
+
+    def gates_tbh(self) -> torch.Tensor:
+        """Activated gates as ``[T, 4, B, H]`` (debug/tests)."""
+        g = self.gates.view(self.T, self.ctas, self.H, 4, 16).permute(0, 3, 1, 4, 2)
+        return g.reshape(self.T, 4, self.ctas * 16, self.H)[:, :, : self.B]
+
+    def c_tbh(self) -> torch.Tensor:
+        """Cell state after every step as ``[T, B, H]`` (debug/tests)."""
+        c = self.c_all.view(self.T, self.ctas, self.H, 16).permute(0, 1, 3, 2)
+        return c.reshape(self.T, self.ctas * 16, self.H)[:, : self.B]
 
 
 def lstm_fwd(x: torch.Tensor, wt: BMat, bias: torch.Tensor, forget_bias: float,

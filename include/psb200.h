@@ -73,10 +73,14 @@ int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, 
  * N dimension, sigmoid/tanh pointwise on the TMEM accumulator, h fed back through shared
  * memory.  `wt` is the cell kernel TRANSPOSED, bf16 [4H, ld_wt] (gate order i,j,f,o); it may
  * point into a peer GPU's memory (the parameter pull is then part of this kernel).
- * Optional outputs: h_last bf16 [B, ld_h], h_last_t bf16 [H, ld_ht]; for training also
- * gates bf16 [T,4,B,H] (activated), c_all fp32 [T,B,H], xh_t bf16 [I+H, ld_xht] whose
+ * Optional outputs: h_last bf16 [B, ld_h], h_last_t bf16 [H, ld_ht]; for training also the
+ * two saved-activation blobs `gates` / `c_all` (opaque, 16-byte aligned, sized by
+ * psb_lstm_saved_bytes, consumed by psb_lstm_bwd) and xh_t bf16 [I+H, ld_xht] whose
  * column t*B+b holds [x_t, h_{t-1}] of batch row b (the weight-gradient GEMM's A operand).
  * ref: rnn.BasicLSTMCell(128, forget_bias=1.0) + rnn.static_rnn, lstm:50-52. */
+/* Bytes of the saved-activation blobs: which = 0 gates (bf16, [t][cta][unit][gate][16]),
+ * which = 1 cell state (fp32, [t][cta][unit][16]); cta = 16 batch rows. */
+size_t psb_lstm_saved_bytes(int B, int T, int H, int which);
 int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const float* bias, float forget_bias,
                  int B, int T, int I, int H, void* h_last, int ld_h, void* h_last_t, int ld_ht,
                  void* gates, float* c_all, void* xh_t, int ld_xht, void* stream);

@@ -33,8 +33,8 @@ def test_lstm_fwd_bwd(B, T, I):
     assert _rel(h_last.float(), h_ref) < 3e-2
     assert _rel(h_last_t.float().t(), h_ref) < 3e-2
     gates_ref = sv.gates.view(T, B, 4, H).permute(0, 2, 1, 3)
-    assert _rel(saved.gates.float(), gates_ref) < 3e-2
-    assert _rel(saved.c_all, sv.c[1:]) < 3e-2
+    assert _rel(saved.gates_tbh().float(), gates_ref) < 3e-2
+    assert _rel(saved.c_tbh(), sv.c[1:]) < 3e-2
     xh_ref = sv.xh.permute(2, 0, 1).reshape(I + H, T * B)
     assert _rel(saved.xh_t.float(), xh_ref) < 3e-2
 
