@@ -26,6 +26,8 @@
 #include "host_common.h"
 #include "ptx.cuh"
 
+#include <mutex>
+
 namespace psb {
 
 constexpr int kPushThreads = 256;
@@ -273,4 +275,122 @@ extern "C" int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void*
     if (!pad || world < 1 || world > 16) return fail(PSB_ERR_ARG, "psb_wait_params: bad argument");
     wait_params_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(pad, world, step_id);
     return after_launch("wait_params");
+}
+
+// ======================================================================================
+// psb_push_apply_noalloc — the same kernel for callers that are not allowed to allocate.
+//
+// psb_push_apply needs three kinds of device memory besides the tensors it works on: the
+// control words the kernel uses as scratch (go flag, finished-block counter, step token),
+// the segment table and the per-rank pointer tables.  Somebody has to cudaMalloc those.
+// Some callers cannot: an optimizer hook that runs inside another framework's memory pool
+// and must not touch the CUDA allocator, a plug-in whose host forbids allocations after
+// start-up, or code on a latency path where an allocation (an implicit device
+// synchronisation) is not acceptable.  For them this entry point keeps all of that in ONE
+// file-scope device array of fixed size, so the library's own image provides the memory:
+// every GPU that loads this library holds sizeof(NoAllocScratch) bytes (about 7 KiB) until
+// the process exits, whether or not this entry point is ever called.
+//
+// What the caller must know
+//   * Limits: at most PSB_NOALLOC_MAX_SEGS (64) segments and PSB_NOALLOC_MAX_WORLD (16)
+//     ranks/arenas; larger requests are refused with PSB_ERR_LIMIT and a message.
+//   * The segment table and the pointer tables are passed as HOST arrays and copied into the
+//     scratch with cudaMemcpyAsync on `stream` before the launch.  Pageable arrays may be
+//     reused as soon as the call returns; pinned arrays must stay unchanged until the stream
+//     has passed the copies.
+//   * The first call on each device looks up the device address of the array
+//     (cudaGetSymbolAddress, with that device current) and caches it.  Make that first call
+//     outside any stream capture.
+//   * All calls on a device share the one array and it keeps what the previous call left
+//     there.  The finished-block counter is cleared on every call; the go flag and the step
+//     token are deliberately kept, because the multi-GPU handshake compares against them.
+//     Two calls that overlap on the GPU (different streams, or graphs replayed concurrently)
+//     race on the array: serialise them.
+//   * Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
+namespace psb {
+
+struct NoAllocScratch {
+    uint32_t ctrl[64];                                  // [0] go flag [1] finished blocks [2] step token
+    psb_push_seg_t segs[PSB_NOALLOC_MAX_SEGS];
+    const float* grad_ptrs[PSB_NOALLOC_MAX_WORLD];
+    void* arena_ptrs[PSB_NOALLOC_MAX_WORLD];
+    float* farena_ptrs[PSB_NOALLOC_MAX_WORLD];
+    uint32_t* pad_ptrs[PSB_NOALLOC_MAX_WORLD];
+};
+
+// In host code this name is only a handle for cudaGetSymbolAddress; the device address it
+// resolves to is what gets passed to the kernel.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[sizeof(NoAllocScratch)];
+
+static int noalloc_scratch_for_current_device(NoAllocScratch** out) {
+    constexpr int kMaxDevices = 64;
+    static NoAllocScratch* cache[kMaxDevices] = {nullptr};
+    static std::mutex mu;
+    int dev = -1;
+    PSB_CUDA_OK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) return fail(PSB_ERR_LIMIT, "psb_push_apply_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (cache[dev] == nullptr) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return fail(PSB_ERR_CUDA, "psb_push_apply_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                        cudaGetErrorString(e));
+        cache[dev] = static_cast<NoAllocScratch*>(p);
+    }
+    *out = cache[dev];
+    return PSB_OK;
+}
+
+}  // namespace psb
+
+extern "C" int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
+                                      const float* const* host_grad_ptrs, void* const* host_arena_ptrs,
+                                      float* const* host_farena_ptrs, uint32_t* const* host_pad_ptrs,
+                                      const psb_push_desc_t* d, void* stream) {
+    using namespace psb;
+    if (!d) return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: null descriptor");
+    if (nseg < 0 || (nseg > 0 && !host_segs)) return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: bad segment table");
+    if (nseg > PSB_NOALLOC_MAX_SEGS)
+        return fail(PSB_ERR_LIMIT, "psb_push_apply_noalloc: %d segments exceed the static scratch (max %d)", nseg,
+                    PSB_NOALLOC_MAX_SEGS);
+    if (d->world < 1 || d->rank < 0 || d->rank >= d->world)
+        return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: need world >= 1 and 0 <= rank < world");
+    const int n_arenas = d->n_arenas > 0 ? d->n_arenas : d->world;
+    if (d->world > PSB_NOALLOC_MAX_WORLD || n_arenas > PSB_NOALLOC_MAX_WORLD)
+        return fail(PSB_ERR_LIMIT, "psb_push_apply_noalloc: world %d / arenas %d exceed the static scratch (max %d)",
+                    d->world, n_arenas, PSB_NOALLOC_MAX_WORLD);
+    if (!host_grad_ptrs || !host_arena_ptrs || !host_farena_ptrs)
+        return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: null pointer table");
+    if (d->world > 1 && !host_pad_ptrs) return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: world > 1 needs signal pads");
+    if (d->nbeta < 0 || d->nbeta > 2) return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: at most two Adam optimizers");
+    int gx = d->blocks_per_seg > 0 ? d->blocks_per_seg : 16;
+    if (gx > 64) gx = 64;
+    dim3 grid(gx, nseg > 0 ? nseg : 1);
+    if (grid.x * grid.y > 148)
+        return fail(PSB_ERR_LIMIT, "psb_push_apply_noalloc: grid %u x %u would not be co-resident", grid.x, grid.y);
+
+    NoAllocScratch* sc = nullptr;
+    int rc = noalloc_scratch_for_current_device(&sc);
+    if (rc != PSB_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    // stage the tables; clear only what must start at zero (the finished-block counter)
+    if (nseg > 0) PSB_CUDA_OK(cudaMemcpyAsync(sc->segs, host_segs, sizeof(psb_push_seg_t) * nseg, cudaMemcpyHostToDevice, st));
+    PSB_CUDA_OK(cudaMemcpyAsync(sc->grad_ptrs, host_grad_ptrs, sizeof(void*) * d->world, cudaMemcpyHostToDevice, st));
+    PSB_CUDA_OK(cudaMemcpyAsync(sc->arena_ptrs, host_arena_ptrs, sizeof(void*) * n_arenas, cudaMemcpyHostToDevice, st));
+    PSB_CUDA_OK(cudaMemcpyAsync(sc->farena_ptrs, host_farena_ptrs, sizeof(void*) * n_arenas, cudaMemcpyHostToDevice, st));
+    if (host_pad_ptrs)
+        PSB_CUDA_OK(cudaMemcpyAsync(sc->pad_ptrs, host_pad_ptrs, sizeof(void*) * d->world, cudaMemcpyHostToDevice, st));
+    PSB_CUDA_OK(cudaMemsetAsync(&sc->ctrl[1], 0, sizeof(uint32_t), st));
+
+    PushArgs a;
+    a.segs = sc->segs; a.nseg = nseg; a.grad_ptrs = sc->grad_ptrs; a.arena_ptrs = sc->arena_ptrs;
+    a.farena_ptrs = sc->farena_ptrs; a.pad_ptrs = sc->pad_ptrs; a.world = d->world; a.rank = d->rank;
+    a.n_arenas = n_arenas; a.inv_replicas = d->inv_replicas;
+    a.step_id = d->step_id; a.local_ctrl = sc->ctrl;
+    a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
+    a.global_step = d->global_step; a.step_delta = d->step_delta;
+    a.async_sgd_atomic = d->async_sgd_atomic; a.signal_params = d->signal_params;
+    push_apply_kernel<<<grid, kPushThreads, 0, st>>>(a);
+    return after_launch("push_apply_noalloc");
 }

@@ -174,6 +174,28 @@ typedef struct psb_push_desc {
  * memory; see csrc/push.cu.  Allocates nothing.
  * ref: minimize() -> Apply* on the ps + AssignAdd(global_step), encoder:137 gan:158-159 lstm:97. */
 int psb_push_apply(const psb_push_desc_t* desc, void* stream);
+/* psb_push_apply for callers that cannot allocate device memory (an optimizer hook running
+ * inside another framework's memory pool, a plug-in whose host forbids allocation after
+ * start-up, a latency path where cudaMalloc's implicit synchronisation is unacceptable).
+ * This entry point has no counterpart in the reference; it exists only for those callers.
+ * The kernel's control words, the segment table and the pointer tables live in one static
+ * device array inside the library image (about 7 KiB per GPU, held until process exit), so
+ * the tables are given as HOST arrays: host_segs[nseg], and host_grad_ptrs[world],
+ * host_arena_ptrs[n_arenas], host_farena_ptrs[n_arenas], host_pad_ptrs[world] (may be NULL
+ * when world == 1).  Of `desc`, the fields segs, grad_ptrs, arena_ptrs, farena_ptrs,
+ * pad_ptrs and local_ctrl are ignored; all others mean what they mean for psb_push_apply.
+ * Limits: nseg <= PSB_NOALLOC_MAX_SEGS, world and n_arenas <= PSB_NOALLOC_MAX_WORLD; beyond
+ * them the call fails with an error text and launches nothing.
+ * The first call on a device resolves the array's device address and caches it: make that
+ * call before any stream capture.  Calls on one device share the array (the finished-block
+ * counter is cleared per call, the step token is kept), so calls that overlap on the GPU
+ * race: serialise them.  Calls no cudaMalloc/cudaFree and no allocating library routine. */
+#define PSB_NOALLOC_MAX_SEGS 64
+#define PSB_NOALLOC_MAX_WORLD 16
+int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
+                           const float* const* host_grad_ptrs, void* const* host_arena_ptrs,
+                           float* const* host_farena_ptrs, uint32_t* const* host_pad_ptrs,
+                           const psb_push_desc_t* desc, void* stream);
 /* Block the stream until every rank has published params-ready >= step_id on `pad`. */
 int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream);
 
