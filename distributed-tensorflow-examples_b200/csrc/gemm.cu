@@ -66,7 +66,7 @@ __device__ __forceinline__ float warp_transpose_reduce(float (&v)[32], uint32_t 
 
 template <int BN>
 __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, float (&v)[32], int row, int n_base,
-                                               int M, int N, uint32_t lane) {
+                                               int M, int N, uint32_t lane, float* s_col_q) {
     const bool row_ok = row < M;
     // ---- bias + activation
 #pragma unroll
@@ -139,11 +139,9 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, float (&v)[32],
         }
     }
     // ---- column sums (bias gradient)
-    if (e.colsum != nullptr) {
-        float s = warp_transpose_reduce(v, lane);
-        const int n = n_base + static_cast<int>(lane);
-        if (n < N) atomicAdd(e.colsum + n, s);
-    }
+    // (per-warp partials go to shared memory; the CTA adds its four row-quadrants in a fixed
+    //  order and issues ONE atomic per column, so two M-tiles still sum deterministically)
+    if (e.colsum != nullptr) s_col_q[lane] = warp_transpose_reduce(v, lane);
 }
 
 template <int BN>
@@ -160,6 +158,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     __shared__ __align__(8) uint64_t empty_bar[8];
     __shared__ __align__(8) uint64_t tmem_full_bar;
     __shared__ uint32_t tmem_base_slot;
+    __shared__ float s_col[4][BN < 32 ? 32 : BN];
 
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t lane = lane_id();
@@ -238,7 +237,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                 float v[32];
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-                epilogue_chunk<BN>(epi, v, row, n0 + c, M, N, lane);
+                epilogue_chunk<BN>(epi, v, row, n0 + c, M, N, lane, &s_col[quad][c]);
             }
         } else {
             uint32_t r[16];
@@ -250,7 +249,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
             for (int j = 16; j < 32; ++j) v[j] = 0.0f;
             // columns 16..31 are beyond this tile: treat them as outside the matrix
-            epilogue_chunk<BN>(epi, v, row, n0, M, (N < n0 + 16) ? N : n0 + 16, lane);
+            epilogue_chunk<BN>(epi, v, row, n0, M, (N < n0 + 16) ? N : n0 + 16, lane, &s_col[quad][0]);
+        }
+        if (epi.colsum != nullptr) {
+            asm volatile("bar.sync 1, 128;" ::: "memory");      // the four epilogue warps only
+            const int te = static_cast<int>(threadIdx.x) - 64;   // 0..127
+            const int ncols = (((N + 7) & ~7) - n0) < BN ? (((N + 7) & ~7) - n0) : BN;
+            for (int c = te; c < BN && c < ((ncols + 31) & ~31); c += 128) {
+                const float s = ((s_col[0][c] + s_col[1][c]) + s_col[2][c]) + s_col[3][c];
+                if (n0 + c < N) atomicAdd(epi.colsum + n0 + c, s);
+            }
         }
         tc_fence_before_sync();
     }

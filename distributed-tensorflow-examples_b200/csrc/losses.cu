@@ -52,29 +52,45 @@ __global__ void __launch_bounds__(256) cast_transpose_kernel(const float* __rest
 // ---------------------------------------------------------------- MSE on sigmoid outputs
 // y fp32 [M, ld_y] = sigmoid output, target fp32 [M, ld_x]:
 //   loss += sum((y-x)^2) / (M*N);  dz = 2 (y-x)/(M*N) * y (1-y)
+// One block owns a 32-column strip for ALL rows, so the bias gradient (column sums) is
+// accumulated in a fixed order without atomics (deterministic).
 __global__ void __launch_bounds__(256) mse_sigmoid_grad_kernel(const float* __restrict__ y, int ld_y,
                                                                const float* __restrict__ x, int ld_x, int M, int N,
                                                                float* loss, __nv_bfloat16* dz, int ld_dz,
                                                                __nv_bfloat16* dz_t, int ld_dzt, float* colsum) {
     __shared__ float tile[32][33];
     __shared__ float red[8];
-    const int n0 = blockIdx.x * 32, m0 = blockIdx.y * 32;
+    const int n0 = blockIdx.x * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const float inv = 1.0f / (static_cast<float>(M) * static_cast<float>(N));
-    float part = 0.0f;
+    float part = 0.0f, csum = 0.0f;
+    for (int m0 = 0; m0 < M; m0 += 32) {
 #pragma unroll
-    for (int r = ty; r < 32; r += 8) {
-        const int m = m0 + r, n = n0 + tx;
-        float g = 0.0f;
-        if (m < M && n < N) {
-            const float yv = y[static_cast<size_t>(m) * ld_y + n];
-            const float d = yv - x[static_cast<size_t>(m) * ld_x + n];
-            part += d * d;
-            g = 2.0f * d * inv * yv * (1.0f - yv);
+        for (int r = ty; r < 32; r += 8) {
+            const int m = m0 + r, n = n0 + tx;
+            float g = 0.0f;
+            if (m < M && n < N) {
+                const float yv = y[static_cast<size_t>(m) * ld_y + n];
+                const float d = yv - x[static_cast<size_t>(m) * ld_x + n];
+                part += d * d;
+                g = 2.0f * d * inv * yv * (1.0f - yv);
+            }
+            tile[r][tx] = g;
+            if (dz != nullptr && m < M && n < ld_dz) dz[static_cast<size_t>(m) * ld_dz + n] = __float2bfloat16_rn(g);
         }
-        tile[r][tx] = g;
-        if (dz != nullptr && m < M && n < ld_dz) dz[static_cast<size_t>(m) * ld_dz + n] = __float2bfloat16_rn(g);
+        __syncthreads();
+#pragma unroll
+        for (int r = ty; r < 32; r += 8) {
+            const int n = n0 + r, m = m0 + tx;
+            if (dz_t != nullptr && n < N && m < M) dz_t[static_cast<size_t>(n) * ld_dzt + m] = __float2bfloat16_rn(tile[tx][r]);
+        }
+        if (ty == 0) {
+#pragma unroll
+            for (int r = 0; r < 32; ++r) csum += tile[r][tx];
+        }
+        __syncthreads();
     }
+    if (colsum != nullptr && ty == 0 && n0 + tx < N) colsum[n0 + tx] += csum;
     part = warp_sum(part);
     if (tx == 0) red[ty] = part;
     __syncthreads();
@@ -83,17 +99,6 @@ __global__ void __launch_bounds__(256) mse_sigmoid_grad_kernel(const float* __re
 #pragma unroll
         for (int i = 0; i < 8; ++i) s += red[i];
         atomicAdd(loss, s * inv);
-    }
-#pragma unroll
-    for (int r = ty; r < 32; r += 8) {
-        const int n = n0 + r, m = m0 + tx;
-        if (dz_t != nullptr && n < N && m < M) dz_t[static_cast<size_t>(n) * ld_dzt + m] = __float2bfloat16_rn(tile[tx][r]);
-    }
-    if (colsum != nullptr && ty == 0) {
-        float s = 0.0f;
-#pragma unroll
-        for (int r = 0; r < 32; ++r) s += tile[r][tx];
-        if (n0 + tx < N) atomicAdd(colsum + n0 + tx, s);
     }
 }
 
@@ -238,7 +243,7 @@ extern "C" int psb_mse_sigmoid_grad(const float* y, int ld_y, const float* x, in
     using namespace psb;
     if (!y || !x || !loss || M < 1 || N < 1) return fail(PSB_ERR_ARG, "psb_mse_sigmoid_grad: bad argument");
     const int ncols = dz ? (ld_dz > N ? ld_dz : N) : N;
-    dim3 grid((ncols + 31) / 32, (M + 31) / 32);
+    dim3 grid((ncols + 31) / 32, 1);
     mse_sigmoid_grad_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         y, ld_y, x, ld_x, M, N, loss, static_cast<__nv_bfloat16*>(dz), ld_dz,
         static_cast<__nv_bfloat16*>(dz_t), ld_dzt, colsum);

@@ -282,7 +282,8 @@ struct LstmBwdArgs {
     int B, T, I;
     __nv_bfloat16* dg_t;         // [4H, ld_dgt] bf16: row g*H+u, column t*B + b
     int ld_dgt;
-    float* dbias;                // [4H] fp32, atomicAdd
+    float* dbias;                // [4H] fp32, += sum over CTAs in CTA order
+    float* dbias_part;           // scratch [gridDim.x][4H] fp32 + 1 counter word at the end
 };
 
 __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a) {
@@ -451,8 +452,18 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
             }
         }
         if (a.dbias != nullptr) {
+            // both halves of the batch slice -> one partial per (cta, gate, unit), summed in a
+            // fixed order so the bias gradient is bit-reproducible
+            float* part = a.dbias_part + static_cast<size_t>(blockIdx.x) * 4 * kH;
+            if (half == 1) {
 #pragma unroll
-            for (int g = 0; g < 4; ++g) atomicAdd(a.dbias + g * kH + u, dbs[g]);
+                for (int g = 0; g < 4; ++g) part[g * kH + u] = dbs[g];
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            if (half == 0) {
+#pragma unroll
+                for (int g = 0; g < 4; ++g) part[g * kH + u] += dbs[g];
+            }
         }
         tc_fence_before_sync();
     }
@@ -460,6 +471,26 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     if (warp == 8) {
         tc_fence_after_sync();
         tmem_dealloc<32>(tmem);
+    }
+    if (a.dbias != nullptr) {
+        // the last CTA to get here adds the per-CTA partials in CTA order
+        __shared__ bool last;
+        unsigned int* counter = reinterpret_cast<unsigned int*>(a.dbias_part + static_cast<size_t>(gridDim.x) * 4 * kH);
+        if (tid == 0) {
+            __threadfence();
+            last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+        }
+        __syncthreads();
+        if (last) {
+            __threadfence();
+            for (int i = tid; i < 4 * kH; i += kLstmThreads) {
+                float s = 0.0f;
+                for (unsigned int cta = 0; cta < gridDim.x; ++cta)
+                    s += *reinterpret_cast<volatile float*>(a.dbias_part + static_cast<size_t>(cta) * 4 * kH + i);
+                a.dbias[i] += s;
+            }
+            if (tid == 0) *counter = 0;
+        }
     }
 }
 
@@ -505,17 +536,18 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
 
 extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const void* gates,
                             const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
-                            float* dbias, void* stream) {
+                            float* dbias, float* dbias_scratch, void* stream) {
     using namespace psb;
     if (H != kH) return fail(PSB_ERR_ARG, "psb_lstm_bwd: this kernel is built for H=128 (got %d)", H);
     if (!w || !dh_last || !gates || !c_all || B < 1 || T < 1) return fail(PSB_ERR_ARG, "psb_lstm_bwd: bad argument");
     if (ld_w % 8 || ld_w < 4 * H) return fail(PSB_ERR_ARG, "psb_lstm_bwd: ld_w must be a multiple of 8 covering 4H");
     if (dg_t && (ld_dgt % 8 || B % 8)) return fail(PSB_ERR_ARG, "psb_lstm_bwd: dg_t needs B%%8==0 and ld_dgt%%8==0");
+    if (dbias && !dbias_scratch) return fail(PSB_ERR_ARG, "psb_lstm_bwd: dbias needs dbias_scratch (ceil(B/16)*4H+1 zeroed floats)");
     LstmBwdArgs a;
     a.w = static_cast<const __nv_bfloat16*>(w); a.ld_w = ld_w; a.dh_last = dh_last; a.ld_dh = ld_dh;
     a.gates = static_cast<const uint4*>(gates); a.c_all = reinterpret_cast<const float4*>(c_all);
     a.B = B; a.T = T; a.I = I;
-    a.dg_t = static_cast<__nv_bfloat16*>(dg_t); a.ld_dgt = ld_dgt; a.dbias = dbias;
+    a.dg_t = static_cast<__nv_bfloat16*>(dg_t); a.ld_dgt = ld_dgt; a.dbias = dbias; a.dbias_part = dbias_scratch;
     const size_t smem = kBwdASmem + kBwdBSmem + 1024;
     static bool attr = false;
     if (!attr) {

@@ -121,7 +121,7 @@ _lib.register_signature("psb_lstm_fwd", [c_void_p, c_void_p, c_int, c_void_p, c_
                                          c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p,
                                          c_void_p, c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_lstm_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int,
-                                         c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p])
+                                         c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p])
 _lib.register_signature("psb_cast_transpose", [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                                c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_mse_sigmoid_grad", [c_void_p, c_int, c_void_p, c_int, c_int, c_int,
@@ -148,6 +148,7 @@ class LstmSaved:
         self.c_all = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 1) // 4, dtype=torch.float32, device=device)
         self.xh_t = BMat(I + H, T * B, device)       # [I+H, T*B]
         self.dg_t = BMat(4 * H, T * B, device)       # [4H, T*B]
+        self.dbias_scratch = torch.zeros(self.ctas * 4 * H + 1, dtype=torch.float32, device=device)
 
     def gates_tbh(self) -> torch.Tensor:
         """Activated gates as ``[T, 4, B, H]`` (debug/tests)."""
@@ -184,7 +185,8 @@ def lstm_bwd(w: BMat, dh_last: torch.Tensor, saved: LstmSaved, dbias: torch.Tens
     check(_lib.lib().psb_lstm_bwd(
         w_ptr if w_ptr is not None else w.ptr, w.ld, dh_last.data_ptr(), dh_last.stride(0),
         saved.gates.data_ptr(), saved.c_all.data_ptr(), saved.B, saved.T, saved.I, saved.H,
-        saved.dg_t.ptr, saved.dg_t.ld, dbias.data_ptr(), current_stream_ptr()), "psb_lstm_bwd")
+        saved.dg_t.ptr, saved.dg_t.ld, dbias.data_ptr(), saved.dbias_scratch.data_ptr(),
+        current_stream_ptr()), "psb_lstm_bwd")
 
 
 # --------------------------------------------------------------------------- cast / losses

@@ -87,12 +87,14 @@ int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const float* bias, f
 
 /* BPTT for psb_lstm_fwd when only the last hidden state feeds the loss.  `w` is the cell kernel
  * in its natural layout, bf16 [I+H, ld_w]; dh_last fp32 [B, ld_dh].  Writes the gate gradients
- * transposed, dg_t bf16 [4H, ld_dgt] (column t*B+b), and atomically adds the bias gradient into
- * dbias fp32 [4H].  The kernel gradient is then one GEMM: dK = xh_t * dg_t^T (psb_gemm_bf16).
+ * transposed, dg_t bf16 [4H, ld_dgt] (column t*B+b), and adds the bias gradient into dbias fp32
+ * [4H] (per-CTA partials in dbias_scratch, ceil(B/16)*4H + 1 floats, zero before first use,
+ * summed in CTA order by the last CTA: bit-reproducible).  The kernel gradient is then one
+ * GEMM: dK = xh_t * dg_t^T (psb_gemm_bf16).
  * ref: the gradient graph optimizer.minimize builds for static_rnn, lstm:97. */
 int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const void* gates,
                  const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
-                 float* dbias, void* stream);
+                 float* dbias, float* dbias_scratch, void* stream);
 
 /* ------------------------------------------------------------------ input cast, losses
  * fp32 [M,N] -> bf16 [M, ld_out] (zero pad columns) and/or its transpose bf16 [N, ld_t].

@@ -1,0 +1,40 @@
+"""T3: fused push/pull across GPUs (needs >= 2 devices; each case is a torchrun job)."""
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _run(n, *args, timeout=300):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n),
+           "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
+           os.path.join(ROOT, "tests", "multigpu_worker.py")] + list(args)
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=timeout, cwd=ROOT)
+    assert r.returncode == 0 and "MULTIGPU_OK" in r.stdout, r.stdout[-3000:]
+
+
+@pytest.mark.parametrize("model", ["lstm", "encoder", "gan"])
+def test_sync_push_matches_oracle_and_is_deterministic(model):
+    _run(2, "--model", model, "--mode", "sync")
+
+
+@pytest.mark.parametrize("model", ["lstm", "gan"])
+def test_async_push_counts_every_update(model):
+    _run(2, "--model", model, "--mode", "async")
+
+
+def test_lstm_pull_from_owner():
+    _run(2, "--model", "lstm", "--mode", "sync", "--pull_from_owner", "1")
