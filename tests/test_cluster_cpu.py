@@ -106,3 +106,12 @@ def test_two_ps_placement_and_resume(tmp_path):
     second = _global_steps(w2[0]) + _global_steps(w2[1])
     assert min(second) > saved_step - 1 and max(second) >= saved_step + 10     # continued, not restarted
     assert first_max >= 20
+
+
+def test_launcher_runs_a_whole_cluster(tmp_path):
+    from psb200.launch import launch
+    rc, logs = launch("encoder", workers=2, ps=1, backend="cpu",
+                      extra=["--synthetic", "--num_steps=10", "--save_model_secs=0"],
+                      model_dir=str(tmp_path / "m"), quiet=True, timeout=120)
+    assert rc == 0, logs
+    assert "ps 0: quitting" in logs["ps:0"] and "Total Time:" in logs["worker:1"]

@@ -38,3 +38,17 @@ def test_async_push_counts_every_update(model):
 
 def test_lstm_pull_from_owner():
     _run(2, "--model", "lstm", "--mode", "sync", "--pull_from_owner", "1")
+
+
+def test_nvl_entrypoints_through_the_reference_cli(tmp_path):
+    """examples/distributed_lstm.py --backend=nvl: 1 ps (done-queue only) + 2 GPU workers, sync."""
+    from psb200.launch import launch
+    rc, logs = launch("lstm", workers=2, ps=1, backend="nvl",
+                      extra=["--synthetic", "--sync", "--num_steps=40", "--save_model_secs=1"],
+                      model_dir=str(tmp_path / "m"), quiet=True, timeout=240)
+    assert rc == 0, logs
+    assert "ps 0 received done 1" in logs["ps:0"] and "ps 0: quitting" in logs["ps:0"]
+    for w in ("worker:0", "worker:1"):
+        assert "Global step 40 Local step 39" in logs[w], logs[w][-2000:]
+        assert "Test-Accuracy:" in logs[w]
+    assert any(f.startswith("model.ckpt-") for f in os.listdir(tmp_path / "m"))

@@ -123,3 +123,23 @@ def test_gan_device_noise_changes_every_replay():
         assert z1.min().item() >= -1 and z1.max().item() <= 1 and abs(z1.mean().item()) < 0.05
     finally:
         tr.close()
+
+
+def test_nvl_entrypoint_single_gpu_async_gan(tmp_path):
+    """examples/distributed_gan.py --backend=nvl on one GPU, async, with checkpoint + resume."""
+    from psb200.checkpoint import Saver, latest_checkpoint
+    from psb200.launch import launch
+    md = str(tmp_path / "m")
+    rc, logs = launch("gan", workers=1, ps=1, backend="nvl",
+                      extra=["--synthetic", "--num_steps=30", "--save_model_secs=1"],
+                      model_dir=md, quiet=True, timeout=240)
+    assert rc == 0, logs
+    assert "ps 0: quitting" in logs["ps:0"] and "Global step 30 Local step 14" in logs["worker:0"]
+    latest = latest_checkpoint(md)
+    vals = Saver.restore(latest)
+    assert int(vals["Variable_8"]) >= 30 and len(vals) == 29
+    assert abs(float(vals["beta1_power"]) - 0.9 ** (int(vals["Variable_8"]) // 2 + 1)) < 1e-3
+    rc, logs = launch("gan", workers=1, ps=1, backend="nvl",
+                      extra=["--synthetic", "--num_steps=50", "--save_model_secs=1"],
+                      model_dir=md, quiet=True, timeout=240)
+    assert rc == 0 and "Global step 32 Local step 0" in logs["worker:0"] and "Global step 50" in logs["worker:0"], logs
