@@ -144,10 +144,15 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, float (&v)[32],
     if (e.colsum != nullptr) s_col_q[lane] = warp_transpose_reduce(v, lane);
 }
 
-template <int BN>
+// kPullB: the B operand (a weight matrix) is NOT staged by TMA from local memory but loaded by
+// the producer warp with 128-bit ld.global from `b_pull` — typically the owner GPU's copy,
+// reached over NVLink — and written into the same 128B-swizzled smem tile.  That is the
+// parameter pull (all-gather) fused into the consuming GEMM: peer loads of stage s+1.. run
+// under the MMAs of stage s.
+template <int BN, bool kPullB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-                 int M, int N, int K, int stages, EpiArgs epi) {
+                 int M, int N, int K, int stages, EpiArgs epi, const __nv_bfloat16* b_pull, int ldb_pull) {
     extern __shared__ uint8_t smem_raw[];
     // 128B-swizzled tiles need 1024-byte alignment
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
@@ -170,7 +175,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         tma_prefetch_desc(&tma_a);
         tma_prefetch_desc(&tma_b);
         for (int s = 0; s < stages; ++s) {
-            mbar_init(&full_bar[s], 1);
+            mbar_init(&full_bar[s], kPullB ? 33 : 1);    // pull: lane 0's expect_tx arrive + 32 loader lanes
             mbar_init(&empty_bar[s], 1);
         }
         mbar_init(&tmem_full_bar, 1);
@@ -183,17 +188,57 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     const uint32_t tmem_base = tmem_base_slot;
 
     if (warp == 0) {
-        // ===================== TMA producer =====================
-        if (lane == 0) {
+        // ===================== producer =====================
+        if constexpr (!kPullB) {
+            if (lane == 0) {
+                int s = 0;
+                uint32_t ph = 0;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* a_dst = smem + s * kStage;
+                    uint8_t* b_dst = a_dst + kBM * 128;
+                    mbar_expect_tx(&full_bar[s], kStage);
+                    tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
+                    tma_load_2d(b_dst, &tma_b, &full_bar[s], kb * kBK, n0);
+                    if (++s == stages) { s = 0; ph ^= 1; }
+                }
+            }
+        } else {
             int s = 0;
             uint32_t ph = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
-                mbar_wait(&empty_bar[s], ph ^ 1);
+                if (lane == 0) mbar_wait(&empty_bar[s], ph ^ 1);
+                __syncwarp();
                 uint8_t* a_dst = smem + s * kStage;
                 uint8_t* b_dst = a_dst + kBM * 128;
-                mbar_expect_tx(&full_bar[s], kStage);
-                tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
-                tma_load_2d(b_dst, &tma_b, &full_bar[s], kb * kBK, n0);
+                if (lane == 0) {
+                    mbar_expect_tx(&full_bar[s], kBM * 128);     // A arrives by TMA (local activations)
+                    tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
+                }
+                // B: BN rows x 8 chunks of 16 bytes from the (peer) weight copy, 8 loads in flight per lane
+                constexpr int kChunks = BN * 8;
+#pragma unroll 1
+                for (int base = 0; base < kChunks; base += 32 * 8) {
+                    float4 v[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int idx = base + j * 32 + static_cast<int>(lane);
+                        const int r = idx >> 3, c = idx & 7;
+                        const int n = n0 + r, k = kb * kBK + c * 8;
+                        v[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        if (idx < kChunks && n < N && k < ldb_pull)
+                            v[j] = ld_v4(reinterpret_cast<const float4*>(b_pull + static_cast<size_t>(n) * ldb_pull + k));
+                    }
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int idx = base + j * 32 + static_cast<int>(lane);
+                        const int r = idx >> 3, c = idx & 7;
+                        if (idx < kChunks)
+                            *reinterpret_cast<float4*>(b_dst + r * 128 + ((c ^ (r & 7)) << 4)) = v[j];
+                    }
+                }
+                fence_proxy_async_smem();
+                mbar_arrive(&full_bar[s]);                       // every lane: its part of B is in place
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
         }
@@ -270,36 +315,39 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     }
 }
 
-template <int BN>
+template <int BN, bool kPullB>
 static int launch_gemm(const CUtensorMap* ta, const CUtensorMap* tb, int M, int N, int K,
-                       const EpiArgs& e, cudaStream_t st) {
+                       const EpiArgs& e, cudaStream_t st, const __nv_bfloat16* b_pull, int ldb_pull) {
     const int num_kb = (K + kBK - 1) / kBK;
     const int stages = pick_stages(BN, num_kb);
     const size_t smem = static_cast<size_t>(stages) * stage_bytes(BN) + 1024;
     static bool attr_set = false;  // per instantiation
     if (!attr_set) {
-        PSB_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<BN>,
+        PSB_CUDA_OK(cudaFuncSetAttribute(gemm_bf16_kernel<BN, kPullB>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
         attr_set = true;
     }
     dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM);
-    gemm_bf16_kernel<BN><<<grid, kGemmThreads, smem, st>>>(*ta, *tb, M, N, K, stages, e);
-    return after_launch("gemm_bf16");
+    gemm_bf16_kernel<BN, kPullB><<<grid, kGemmThreads, smem, st>>>(*ta, *tb, M, N, K, stages, e, b_pull, ldb_pull);
+    return after_launch(kPullB ? "gemm_bf16_pull" : "gemm_bf16");
 }
 
 }  // namespace psb
 
-extern "C" int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
-                             const psb_epilogue_t* epi, int block_n, void* stream) {
+static int gemm_entry(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                      const psb_epilogue_t* epi, int block_n, void* stream, bool pull) {
     using namespace psb;
-    if (!A || !B || !epi) return fail(PSB_ERR_ARG, "psb_gemm_bf16: null pointer argument");
-    if (M <= 0 || N <= 0 || K <= 0) return fail(PSB_ERR_ARG, "psb_gemm_bf16: M, N, K must be positive");
-    if (lda < K || ldb < K) return fail(PSB_ERR_ARG, "psb_gemm_bf16: leading dimension smaller than K");
+    const char* who = pull ? "psb_gemm_bf16_pull" : "psb_gemm_bf16";
+    if (!A || !B || !epi) return fail(PSB_ERR_ARG, "%s: null pointer argument", who);
+    if (M <= 0 || N <= 0 || K <= 0) return fail(PSB_ERR_ARG, "%s: M, N, K must be positive", who);
+    if (lda < K || ldb < K) return fail(PSB_ERR_ARG, "%s: leading dimension smaller than K", who);
     if (epi->yprev && (epi->ld_yprev % 8 || epi->dact < 1 || epi->dact > 2))
-        return fail(PSB_ERR_ARG, "psb_gemm_bf16: yprev needs ld%%8==0 and dact in {1,2}");
-    if (epi->out && epi->ld_out % 8) return fail(PSB_ERR_ARG, "psb_gemm_bf16: ld_out must be a multiple of 8");
+        return fail(PSB_ERR_ARG, "%s: yprev needs ld%%8==0 and dact in {1,2}", who);
+    if (epi->out && epi->ld_out % 8) return fail(PSB_ERR_ARG, "%s: ld_out must be a multiple of 8", who);
     if (epi->out && epi->ld_out < ((N + 7) & ~7))
-        return fail(PSB_ERR_ARG, "psb_gemm_bf16: ld_out must cover N rounded up to 8");
+        return fail(PSB_ERR_ARG, "%s: ld_out must cover N rounded up to 8", who);
+    if (pull && (ldb % 8 || (reinterpret_cast<uintptr_t>(B) & 15)))
+        return fail(PSB_ERR_ARG, "%s: B must be 16-byte aligned with ldb a multiple of 8", who);
 
     int bn = block_n;
     if (bn == 0) {
@@ -313,8 +361,11 @@ extern "C" int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int
     }
     const CUtensorMap* ta = tensor_map_bf16_2d(A, M, K, lda, kBM);
     if (!ta) return PSB_ERR_DRIVER;
-    const CUtensorMap* tb = tensor_map_bf16_2d(B, N, K, ldb, bn);
-    if (!tb) return PSB_ERR_DRIVER;
+    const CUtensorMap* tb = ta;      // unused by the pull variant
+    if (!pull) {
+        tb = tensor_map_bf16_2d(B, N, K, ldb, bn);
+        if (!tb) return PSB_ERR_DRIVER;
+    }
 
     EpiArgs e;
     e.alpha = epi->alpha;
@@ -331,12 +382,33 @@ extern "C" int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int
     e.ld_f32 = epi->ld_f32;
     e.colsum = epi->colsum;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    switch (bn) {
-        case 16: return launch_gemm<16>(ta, tb, M, N, K, e, st);
-        case 32: return launch_gemm<32>(ta, tb, M, N, K, e, st);
-        case 64: return launch_gemm<64>(ta, tb, M, N, K, e, st);
-        case 128: return launch_gemm<128>(ta, tb, M, N, K, e, st);
-        case 256: return launch_gemm<256>(ta, tb, M, N, K, e, st);
-        default: return fail(PSB_ERR_ARG, "psb_gemm_bf16: block_n must be 0, 16, 32, 64, 128 or 256");
+    const __nv_bfloat16* bp = static_cast<const __nv_bfloat16*>(B);
+    if (pull) {
+        switch (bn) {
+            case 16: return launch_gemm<16, true>(ta, tb, M, N, K, e, st, bp, ldb);
+            case 32: return launch_gemm<32, true>(ta, tb, M, N, K, e, st, bp, ldb);
+            case 64: return launch_gemm<64, true>(ta, tb, M, N, K, e, st, bp, ldb);
+            case 128: return launch_gemm<128, true>(ta, tb, M, N, K, e, st, bp, ldb);
+            case 256: return launch_gemm<256, true>(ta, tb, M, N, K, e, st, bp, ldb);
+            default: return fail(PSB_ERR_ARG, "%s: block_n must be 0, 16, 32, 64, 128 or 256", who);
+        }
     }
+    switch (bn) {
+        case 16: return launch_gemm<16, false>(ta, tb, M, N, K, e, st, nullptr, 0);
+        case 32: return launch_gemm<32, false>(ta, tb, M, N, K, e, st, nullptr, 0);
+        case 64: return launch_gemm<64, false>(ta, tb, M, N, K, e, st, nullptr, 0);
+        case 128: return launch_gemm<128, false>(ta, tb, M, N, K, e, st, nullptr, 0);
+        case 256: return launch_gemm<256, false>(ta, tb, M, N, K, e, st, nullptr, 0);
+        default: return fail(PSB_ERR_ARG, "%s: block_n must be 0, 16, 32, 64, 128 or 256", who);
+    }
+}
+
+extern "C" int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
+                             const psb_epilogue_t* epi, int block_n, void* stream) {
+    return gemm_entry(A, lda, B, ldb, M, N, K, epi, block_n, stream, false);
+}
+
+extern "C" int psb_gemm_bf16_pull(const void* A, int lda, const void* B_peer, int ldb, int M, int N, int K,
+                                  const psb_epilogue_t* epi, int block_n, void* stream) {
+    return gemm_entry(A, lda, B_peer, ldb, M, N, K, epi, block_n, stream, true);
 }

@@ -75,9 +75,9 @@ class EncoderPlan(DevicePlan):
         s, n = self.store, self._name
         K.cast_transpose(self.inputs["x"], self.act[0], self.act_t[0] if need_t else None)
         for l in range(3):
-            K.gemm(self.act[l], s.wt(n(self.wkeys[l])), bias=s.vec(n(self.bkeys[l])), act=ACT_SIGMOID,
+            K.gemm(self.act[l], s.wt_src(n(self.wkeys[l])), bias=s.vec_src(n(self.bkeys[l])), act=ACT_SIGMOID,
                    out=self.act[l + 1], out_t=self.act_t[l + 1] if need_t else None)
-        K.gemm(self.act[3], s.wt(n(self.wkeys[3])), bias=s.vec(n(self.bkeys[3])), act=ACT_SIGMOID,
+        K.gemm(self.act[3], s.wt_src(n(self.wkeys[3])), bias=s.vec_src(n(self.bkeys[3])), act=ACT_SIGMOID,
                out_f32=self.y)
 
     def forward_backward(self) -> None:
@@ -91,7 +91,7 @@ class EncoderPlan(DevicePlan):
             # dW_l = act_{l}^T dz_{l+1}
             K.gemm(self.act_t[l], self.dz_t[l + 1], out_f32=s.grad(n(self.wkeys[l])))
             if l > 0:
-                K.gemm(self.dz[l + 1], s.w(n(self.wkeys[l])), yprev=self.act[l], dact=1,
+                K.gemm(self.dz[l + 1], s.w_src(n(self.wkeys[l])), yprev=self.act[l], dact=1,
                        out=self.dz[l], out_t=self.dz_t[l], colsum=s.grad(n(self.bkeys[l - 1])))
 
     def kernels_per_step(self) -> int:
@@ -136,13 +136,13 @@ class GanPlan(DevicePlan):
                             self.noise_counter, out=self.inputs["z"], out_bf16=self.Z, out_t=self.ZT)
         else:
             K.cast_transpose(self.inputs["z"], self.Z, self.ZT)
-        K.gemm(self.Z, s.wt(n("w_gen_hidden1")), bias=s.vec(n("b_gen_hidden1")), act=ACT_RELU,
+        K.gemm(self.Z, s.wt_src(n("w_gen_hidden1")), bias=s.vec_src(n("b_gen_hidden1")), act=ACT_RELU,
                out=self.GH, out_t=self.GHT)
-        K.gemm(self.GH, s.wt(n("w_gen_out")), bias=s.vec(n("b_gen_out")), act=ACT_SIGMOID,
+        K.gemm(self.GH, s.wt_src(n("w_gen_out")), bias=s.vec_src(n("b_gen_out")), act=ACT_SIGMOID,
                out=self.Din_fake, out_t=self.DinT_fake)
-        K.gemm(self.Din, s.wt(n("w_disc_hidden1")), bias=s.vec(n("b_disc_hidden1")), act=ACT_RELU,
+        K.gemm(self.Din, s.wt_src(n("w_disc_hidden1")), bias=s.vec_src(n("b_disc_hidden1")), act=ACT_RELU,
                out=self.DH, out_t=self.DHT)
-        K.gemm(self.DH, s.wt(n("w_disc_out")), bias=s.vec(n("b_disc_out")), act=ACT_NONE,
+        K.gemm(self.DH, s.wt_src(n("w_disc_out")), bias=s.vec_src(n("b_disc_out")), act=ACT_NONE,
                out_f32=self.logit)
 
     def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
@@ -153,15 +153,15 @@ class GanPlan(DevicePlan):
                         s.grad(n("b_disc_out")) if disc else None)
         if disc:
             K.gemm(self.DHT, self.d_disc_t, out_f32=s.grad(n("w_disc_out")))
-            K.gemm(self.d_disc, s.w(n("w_disc_out")), yprev=self.DH, dact=2, out=self.dZ1, out_t=self.dZ1T,
+            K.gemm(self.d_disc, s.w_src(n("w_disc_out")), yprev=self.DH, dact=2, out=self.dZ1, out_t=self.dZ1T,
                    colsum=s.grad(n("b_disc_hidden1")))
             K.gemm(self.DinT, self.dZ1T, out_f32=s.grad(n("w_disc_hidden1")))
         if gen:
-            K.gemm(self.d_gen, s.w(n("w_disc_out")), yprev=self.DH_fake, dact=2, out=self.dZ1f)
-            K.gemm(self.dZ1f, s.w(n("w_disc_hidden1")), yprev=self.Din_fake, dact=1, out=self.dZo,
+            K.gemm(self.d_gen, s.w_src(n("w_disc_out")), yprev=self.DH_fake, dact=2, out=self.dZ1f)
+            K.gemm(self.dZ1f, s.w_src(n("w_disc_hidden1")), yprev=self.Din_fake, dact=1, out=self.dZo,
                    out_t=self.dZoT, colsum=s.grad(n("b_gen_out")))
             K.gemm(self.GHT, self.dZoT, out_f32=s.grad(n("w_gen_out")))
-            K.gemm(self.dZo, s.w(n("w_gen_out")), yprev=self.GH, dact=2, out=self.dZh, out_t=self.dZhT,
+            K.gemm(self.dZo, s.w_src(n("w_gen_out")), yprev=self.GH, dact=2, out=self.dZh, out_t=self.dZhT,
                    colsum=s.grad(n("b_gen_hidden1")))
             K.gemm(self.ZT, self.dZhT, out_f32=s.grad(n("w_gen_hidden1")))
 
@@ -188,6 +188,7 @@ class LstmPlan(DevicePlan):
         self.dh = torch.zeros(B, H, device=dev)
         # bcast=False stores keep the cell kernel only in its owner's arena: the LSTM kernels
         # then read it through the owner's peer pointer (pull fused into the consumer)
+        pull_from_owner = pull_from_owner or not store.bcast
         self.pull_from_owner = pull_from_owner
         kname = self._name("kernel")
         self._k_owner = store.owner(kname) if pull_from_owner else None
@@ -201,10 +202,10 @@ class LstmPlan(DevicePlan):
     def forward(self, train: bool = False) -> None:
         s, n = self.store, self._name
         wt_ptr, _ = self._kernel_ptrs()
-        K.lstm_fwd(self.inputs["x"], s.wt(n("kernel")), s.vec(n("bias")), lstm_mod.forget_bias,
+        K.lstm_fwd(self.inputs["x"], s.wt(n("kernel")), s.vec_src(n("bias")), lstm_mod.forget_bias,
                    self.h_last, self.h_last_t if train else None, self.saved if train else None,
                    wt_ptr=wt_ptr)
-        K.gemm(self.h_last, s.wt(n("out_w")), bias=s.vec(n("out_b")), out_f32=self.logits)
+        K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits)
 
     def evaluate(self) -> None:
         """Fills ``losses['loss']`` and ``correct`` for the current inputs without touching
@@ -221,7 +222,7 @@ class LstmPlan(DevicePlan):
         K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
                             self.dlogits_t, s.grad(n("out_b")), self.correct)
         K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
-        K.gemm(self.dlogits, s.w(n("out_w")), out_f32=self.dh)
+        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh)
         K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
         K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")))
 

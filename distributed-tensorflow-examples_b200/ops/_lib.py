@@ -42,6 +42,8 @@ def _declare(lib) -> None:
     lib.psb_gemm_bf16.restype = c_int
     lib.psb_gemm_bf16.argtypes = [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int,
                                   POINTER(Epilogue), c_int, c_void_p]
+    lib.psb_gemm_bf16_pull.restype = c_int
+    lib.psb_gemm_bf16_pull.argtypes = lib.psb_gemm_bf16.argtypes
     for name, sig in _EXTRA_SIGNATURES.items():
         fn = getattr(lib, name, None)
         if fn is None:

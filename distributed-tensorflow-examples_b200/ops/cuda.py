@@ -28,10 +28,11 @@ class BMat:
     next GEMM (TMA needs 16-byte row strides: K=100 -> 104, K=156 -> 160, N=1 -> 8).
     """
 
-    __slots__ = ("t", "rows", "cols")
+    __slots__ = ("t", "rows", "cols", "remote")
 
     def __init__(self, rows: int, cols: int, device="cuda", data: Optional[torch.Tensor] = None):
         self.rows, self.cols = int(rows), int(cols)
+        self.remote = False          # True: the storage is another GPU's memory (peer mapping)
         self.t = torch.zeros(self.rows, round_up(self.cols, 8), dtype=torch.bfloat16, device=device)
         if data is not None:
             self.t[:, : self.cols].copy_(data)
@@ -43,7 +44,7 @@ class BMat:
     def rows_view(self, r0: int, r1: int) -> "BMat":
         """Rows ``r0:r1`` as a matrix sharing this storage."""
         m = BMat.__new__(BMat)
-        m.rows, m.cols, m.t = r1 - r0, self.cols, self.t[r0:r1]
+        m.rows, m.cols, m.t, m.remote = r1 - r0, self.cols, self.t[r0:r1], self.remote
         return m
 
     def cols_view(self, c0: int, c1: int) -> "BMat":
@@ -51,7 +52,7 @@ class BMat:
         if c0 % 8:
             raise ValueError("column views must start on a 16-byte boundary")
         m = BMat.__new__(BMat)
-        m.rows, m.cols, m.t = self.rows, c1 - c0, self.t[:, c0:]
+        m.rows, m.cols, m.t, m.remote = self.rows, c1 - c0, self.t[:, c0:], self.remote
         return m
 
     @property
@@ -62,9 +63,9 @@ class BMat:
         return self.t[:, : self.cols].float()
 
     @staticmethod
-    def wrap(t: torch.Tensor, rows: int, cols: int) -> "BMat":
+    def wrap(t: torch.Tensor, rows: int, cols: int, remote: bool = False) -> "BMat":
         m = BMat.__new__(BMat)
-        m.rows, m.cols, m.t = rows, cols, t
+        m.rows, m.cols, m.t, m.remote = rows, cols, t, remote
         return m
 
     @staticmethod
@@ -110,8 +111,13 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
         raise ValueError("gemm: out must be [%d,%d]" % (M, N))
     if out_t is not None and (out_t.rows != N or out_t.cols != M):
         raise ValueError("gemm: out_t must be [%d,%d]" % (N, M))
-    check(_lib.lib().psb_gemm_bf16(a.ptr, a.ld, b.ptr, b.ld, M, N, K, e, block_n,
-                                   current_stream_ptr()), "psb_gemm_bf16")
+    if getattr(b, "remote", False):
+        # the weight copy lives in its owner's HBM: pull it inside the GEMM (no TMA on peer memory)
+        check(_lib.lib().psb_gemm_bf16_pull(a.ptr, a.ld, b.ptr, b.ld, M, N, K, e, block_n,
+                                            current_stream_ptr()), "psb_gemm_bf16_pull")
+    else:
+        check(_lib.lib().psb_gemm_bf16(a.ptr, a.ld, b.ptr, b.ld, M, N, K, e, block_n,
+                                       current_stream_ptr()), "psb_gemm_bf16")
 
 
 # --------------------------------------------------------------------------- LSTM

@@ -203,6 +203,7 @@ class NvlStore:
         L = self.layout[name]
         m = BMat.__new__(BMat)
         m.rows, m.cols = L.rows, L.cols
+        m.remote = rank is not None and rank != self.rank
         m.t = self.heap.tensor(self._arena_off + 2 * L.w_off, (L.rows, L.ld_w), torch.bfloat16, rank)
         return m
 
@@ -211,6 +212,7 @@ class NvlStore:
         L = self.layout[name]
         m = BMat.__new__(BMat)
         m.rows, m.cols = L.cols, L.rows
+        m.remote = rank is not None and rank != self.rank
         m.t = self.heap.tensor(self._arena_off + 2 * L.wt_off, (L.cols, L.ld_wt), torch.bfloat16, rank)
         return m
 
@@ -218,6 +220,20 @@ class NvlStore:
         """fp32 compute copy of a 1-D variable."""
         L = self.layout[name]
         return self.heap.tensor(self._farena_off + 4 * L.f_off, (L.spec.numel,), torch.float32, rank)
+
+    # where a consumer kernel should read a compute copy from: this rank's arena when the push
+    # kernel broadcasts (bcast=True), otherwise the owner's arena through its peer mapping
+    def _src_rank(self, name: str) -> Optional[int]:
+        return None if self.bcast else self.layout[name].owner
+
+    def w_src(self, name: str) -> BMat:
+        return self.w(name, self._src_rank(name))
+
+    def wt_src(self, name: str) -> BMat:
+        return self.wt(name, self._src_rank(name))
+
+    def vec_src(self, name: str) -> torch.Tensor:
+        return self.vec(name, self._src_rank(name))
 
     def grad(self, name: str) -> torch.Tensor:
         L = self.layout[name]

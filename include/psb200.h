@@ -66,6 +66,16 @@ typedef struct psb_epilogue {
 int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const psb_epilogue_t* epi, int block_n /*0 = auto*/, void* stream);
 
+/* Parameter pull fused into the consuming GEMM.  Same contract as psb_gemm_bf16, but B (the
+ * weight copy, [N, ldb] bf16, pad columns zero) may live in ANOTHER GPU's memory: the producer
+ * warp fetches each B tile with 128-bit loads over NVLink straight into the swizzled
+ * shared-memory stage (no TMA descriptor on the peer address, no local staging copy) while
+ * the tensor cores work on the previous stages; A still arrives by TMA from local memory.
+ * `epi->bias` may be a peer pointer too.
+ * ref: the per-step ps->worker variable reads TF inserts for encoder:69-83, gan:77-90, lstm:53. */
+int psb_gemm_bf16_pull(const void* A, int lda, const void* B_peer, int ldb, int M, int N, int K,
+                       const psb_epilogue_t* epi, int block_n /*0 = auto*/, void* stream);
+
 
 /* ------------------------------------------------------------------ persistent LSTM (H = 128)
  * Forward: BasicLSTMCell unrolled over T steps from a zero state, one CTA per 16 batch rows,

@@ -77,3 +77,21 @@ def test_gemm_dact_colsum(dact):
     assert (out.float() - ref).abs().max().item() < 2e-2 * scale
     assert (out_t.float().t() - ref).abs().max().item() < 2e-2 * scale
     assert (colsum - ref.sum(0)).abs().max().item() < 1e-2 * max(1.0, ref.sum(0).abs().max().item())
+
+
+@pytest.mark.parametrize("M,N,K,bn", [(256, 256, 784, 0), (128, 784, 256, 64), (128, 1, 256, 0),
+                                      (128, 256, 100, 32), (300, 520, 456, 128), (256, 512, 1024, 256)])
+def test_gemm_pull_variant_matches(M, N, K, bn):
+    """psb_gemm_bf16_pull (B fetched by ld.global into swizzled smem) == the TMA kernel == oracle."""
+    from psb200.ops import cuda as K_
+    a, b = _mats(M, N, K, 3)
+    bias = torch.randn(N, device="cuda")
+    A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
+    o1, o2 = K_.BMat(M, N), K_.BMat(M, N)
+    K_.gemm(A, B, bias=bias, act=1, out=o1, block_n=bn)
+    B.remote = True
+    K_.gemm(A, B, bias=bias, act=1, out=o2, block_n=bn)
+    torch.cuda.synchronize()
+    ref = torch.sigmoid(A.float() @ B.float().t() + bias)
+    assert (o2.float() - ref).abs().max().item() < 2e-2
+    assert torch.equal(o1.t, o2.t)

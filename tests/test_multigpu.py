@@ -36,8 +36,11 @@ def test_async_push_counts_every_update(model):
     _run(2, "--model", model, "--mode", "async")
 
 
-def test_lstm_pull_from_owner():
-    _run(2, "--model", "lstm", "--mode", "sync", "--pull_from_owner", "1")
+@pytest.mark.parametrize("model", ["lstm", "encoder", "gan"])
+def test_pull_fused_into_consumer_kernels(model):
+    """bcast=False: compute copies stay in the owner's arena; the LSTM kernels and the dense GEMMs
+    (psb_gemm_bf16_pull) read them through peer pointers."""
+    _run(2, "--model", model, "--mode", "sync", "--pull_from_owner", "1")
 
 
 def test_nvl_entrypoints_through_the_reference_cli(tmp_path):
