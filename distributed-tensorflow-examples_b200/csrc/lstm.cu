@@ -3,8 +3,9 @@
 // "Swap-AB" formulation so that a small batch slice becomes the MMA N dimension:
 //
 //   forward, per timestep:   gates^T[4H, nb] = Wt[4H, I+H] * xh_t^T[I+H, nb]
-//       A = Wt (the cell kernel transposed, bf16, resident in shared memory for the whole
-//           sequence), B = [x_t, h_{t-1}] of this CTA's 16 batch rows, D in TMEM:
+//       A = Wt (the cell kernel transposed, bf16, resident in TENSOR MEMORY for the whole
+//           sequence: 4 gates x 80 columns, so an MMA never re-reads the weights from shared
+//           memory), B = [x_t, h_{t-1}] of this CTA's 16 batch rows, D in TMEM:
 //           gate g occupies TMEM columns [16g, 16g+16), lane = hidden unit.
 //       256 pointwise threads (thread = hidden unit x half of the batch slice) read i,j,f,o
 //       for their unit from TMEM, do the sigmoid/tanh math with c held in registers, and
@@ -15,11 +16,12 @@
 //       MMA of step t is in flight.
 //
 // One CTA per 16 batch rows, no inter-CTA synchronisation; the sequence loop never leaves
-// the SM.  The weight load at kernel start is cp.async from plain global addresses, so the
+// the SM.  The weight load at kernel start is plain 128-bit ld.global + tcgen05.st, so the
 // weight pointer may be a peer GPU's HBM (parameter pull fused into the consuming kernel).
 //
-// Saved-for-backward blobs (private layout shared by the two kernels, 16-byte vectors per
-// thread):   gates[t][cta][u][g][16] bf16 (activated i,j,f,o)     c[t][cta][u][16] fp32
+// Saved-for-backward blobs (private layout shared by the two kernels; 16-byte vectors, unit
+// index fastest so that a warp's store/load is one contiguous 512-byte run):
+//   gates[t][cta][g][half][u][8] bf16 (activated i,j,f,o)     c[t][cta][half][2][u][4] fp32
 //
 // ref: rnn.BasicLSTMCell(num_hidden, forget_bias=1.0) + rnn.static_rnn, lstm:50-52, and the
 //      backward that optimizer.minimize builds for it, lstm:97.
@@ -34,12 +36,14 @@ constexpr int kNB = 16;              // batch rows per CTA (UMMA N)
 constexpr int kHB = 8;               // batch rows per pointwise thread
 constexpr int kPW = 256;             // pointwise threads (8 warps)
 constexpr int kLstmThreads = kPW + 32;   // + 1 MMA warp
-constexpr int kFwdKB = 3;            // k-blocks of 64 covering I+H <= 192
-constexpr int kFwdASmem = kFwdKB * 4 * kH * 128;   // 196608
-constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144
+constexpr int kFwdKB = 3;            // k-blocks of 64 covering I+H <= 160 (+pad)
+constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144: the [x_t, h_{t-1}] operand
+constexpr int kFwdKMax = 160;        // I + H <= 160: 80 TMEM columns per gate block
+constexpr uint32_t kFwdAcc = 0;      // TMEM columns [0, 64): gate accumulators
+constexpr uint32_t kFwdW = 64;       // TMEM columns [64, 64 + 4*80): the cell kernel (A operand)
 constexpr int kBwdKB = 8;            // 4H / 64
-constexpr int kBwdASmem = kBwdKB * kH * 128;       // 131072
-constexpr int kBwdBSmem = kBwdKB * kNB * 128;      // 16384
+constexpr int kBwdBSmem = kBwdKB * kNB * 128;      // 16384: the dG_t operand
+constexpr uint32_t kBwdW = 32;       // TMEM columns [32, 32 + 256): Wh (A operand); [0,16): dh accumulator
 
 __device__ __forceinline__ float sigmoid_t(float x) { return fmaf(0.5f, fast_tanh(0.5f * x), 0.5f); }
 
@@ -75,8 +79,7 @@ struct LstmFwdArgs {
 __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint8_t* sA = smem;
-    uint8_t* sB = smem + kFwdASmem;
+    uint8_t* sB = smem;
     __shared__ __align__(8) uint64_t xh_ready, mma_done;
     __shared__ uint32_t tmem_slot;
 
@@ -85,26 +88,42 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
     const int K = a.I + kH;
 
     if (tid == 0) {
-        mbar_init(&xh_ready, kPW);
+        mbar_init(&xh_ready, kPW / 32);       // one arrival per pointwise warp
         mbar_init(&mma_done, 1);
         fence_mbar_init();
     }
-    if (warp == 8) tmem_alloc<64>(&tmem_slot);
+    if (warp == 8) tmem_alloc<512>(&tmem_slot);
+    for (int idx = tid; idx < kFwdBSmem / 16; idx += kLstmThreads)
+        reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
+    tc_fence_before_sync();
+    __syncthreads();   // sB zeroed before x_0 goes in; TMEM base address published
+    tc_fence_after_sync();
+    const uint32_t tmem = tmem_slot;
 
-    // ---- weights: global (possibly peer) -> swizzled shared, 16 bytes per cp.async
-    {
-        const int chunks_per_row = kFwdKB * 8;                 // 24 chunks of 8 bf16
-        const int total = 4 * kH * chunks_per_row;
-        for (int idx = tid; idx < total; idx += kLstmThreads) {
-            const int r = idx / chunks_per_row, c = idx % chunks_per_row;
-            uint8_t* dst = sA + swz_off(4 * kH, r, c * 8);
-            if (c * 8 < a.ld_wt) cp_async_16(dst, a.wt + static_cast<size_t>(r) * a.ld_wt + c * 8);
-            else *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+    // ---- weights: global (possibly a peer GPU) -> registers -> TMEM, where they stay for the
+    // whole sequence as the A operand.  Thread (u, half) owns row g*H+u of gates 2*half, 2*half+1.
+    if (warp < 8) {
+        const int u = static_cast<int>(tid & 127), half = static_cast<int>(tid >> 7);
+        const uint32_t lane_base = tmem + (((warp & 3u) * 32u) << 16);
+#pragma unroll 1
+        for (int gg = 0; gg < 2; ++gg) {
+            const int g = 2 * half + gg;
+            const __nv_bfloat16* row = a.wt + static_cast<size_t>(g * kH + u) * a.ld_wt;
+#pragma unroll 1
+            for (int c16 = 0; c16 < kFwdKMax / 32; ++c16) {       // 32 bf16 = 16 TMEM columns per batch
+                uint32_t r[16];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int k = c16 * 32 + q * 8;
+                    uint4 v = make_uint4(0, 0, 0, 0);
+                    if (k < a.ld_wt) v = *reinterpret_cast<const uint4*>(row + k);
+                    r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
+                }
+                tmem_st_32x16(lane_base + kFwdW + g * (kFwdKMax / 2) + c16 * 16, r);
+            }
         }
-        for (int idx = tid; idx < kFwdBSmem / 16; idx += kLstmThreads)
-            reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
+        tmem_st_wait();
     }
-    __syncthreads();   // sB zeroed before x_0 goes in
 
     const int x_per_step = kNB * a.I;      // <= 512 elements of x per step for this CTA
     if (warp < 8) {
@@ -116,31 +135,34 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
             if (a.xh_t != nullptr && b0 + b < a.B) a.xh_t[static_cast<size_t>(i) * a.ld_xht + b0 + b] = xb;
         }
     }
-    cp_async_wait_all();
     fence_proxy_async_smem();
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
-    const uint32_t tmem = tmem_slot;
 
     if (warp == 8) {
         // ===================== MMA issuer =====================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
-            const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
-            const int ksteps = (K + 15) >> 4;
+            const uint32_t b_base = smem_u32(sB);
+            const int ksteps = (K + 15) >> 4;                    // <= 10
+            uint64_t db[kFwdKMax / 16];                           // loop-invariant B descriptors
+#pragma unroll
+            for (int ks = 0; ks < kFwdKMax / 16; ++ks)
+                db[ks] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
+            const uint32_t acc = tmem + kFwdAcc, wbase = tmem + kFwdW;
             for (int t = 0; t < a.T; ++t) {
                 if (t > 0) {
                     mbar_wait(&xh_ready, (t - 1) & 1);
                     tc_fence_after_sync();
                 }
-                for (int ks = 0; ks < ksteps; ++ks) {
-                    const int kb = ks >> 2, k4 = ks & 3;
-                    const uint64_t db = umma_desc_k128(b_base + kb * (kNB * 128)) + 2 * k4;
 #pragma unroll
-                    for (int g = 0; g < 4; ++g) {
-                        const uint64_t da = umma_desc_k128(a_base + kb * (4 * kH * 128) + g * (kH * 128)) + 2 * k4;
-                        umma_bf16(tmem + g * kNB, da, db, idesc, ks != 0 ? 1u : 0u);
+                for (int ks = 0; ks < kFwdKMax / 16; ++ks) {
+                    if (ks < ksteps) {
+#pragma unroll
+                        for (int g = 0; g < 4; ++g)
+                            umma_bf16_ts(acc + g * kNB, wbase + g * (kFwdKMax / 2) + ks * 8, db[ks], idesc,
+                                         ks != 0 ? 1u : 0u);
                     }
                 }
                 umma_commit(&mma_done);
@@ -155,7 +177,6 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
         const float bi = a.bias[u], bj = a.bias[kH + u], bf = a.bias[2 * kH + u] + a.forget_bias,
                     bo = a.bias[3 * kH + u];
         const bool full = (b0 + kNB <= a.B);
-        const size_t blob_row = static_cast<size_t>(gridDim.x) * kH;     // (cta,u) rows per timestep
         float c[kHB];
 #pragma unroll
         for (int b = 0; b < kHB; ++b) c[b] = 0.0f;
@@ -216,24 +237,25 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
                 }
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
-                mbar_arrive(&xh_ready);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&xh_ready);
             }
             // ---- everything below is off the recurrence's critical path
             if (a.gates != nullptr) {
-                const size_t row = static_cast<size_t>(t) * blob_row + static_cast<size_t>(blockIdx.x) * kH + u;
-                uint4* gp = a.gates + row * 8 + half;            // 8 uint4 per (t,cta,u): [g][2 halves]
+                const size_t blk = static_cast<size_t>(t) * gridDim.x + blockIdx.x;
+                uint4* gp = a.gates + blk * (8 * kH) + half * kH + u;      // + g * 2 * kH per gate
                 uint4 v;
                 v.x = pack_bf16(ig[0], ig[1]); v.y = pack_bf16(ig[2], ig[3]); v.z = pack_bf16(ig[4], ig[5]); v.w = pack_bf16(ig[6], ig[7]);
                 gp[0] = v;
                 v.x = pack_bf16(jg[0], jg[1]); v.y = pack_bf16(jg[2], jg[3]); v.z = pack_bf16(jg[4], jg[5]); v.w = pack_bf16(jg[6], jg[7]);
-                gp[2] = v;
+                gp[2 * kH] = v;
                 v.x = pack_bf16(fg[0], fg[1]); v.y = pack_bf16(fg[2], fg[3]); v.z = pack_bf16(fg[4], fg[5]); v.w = pack_bf16(fg[6], fg[7]);
-                gp[4] = v;
+                gp[4 * kH] = v;
                 v.x = pack_bf16(og[0], og[1]); v.y = pack_bf16(og[2], og[3]); v.z = pack_bf16(og[4], og[5]); v.w = pack_bf16(og[6], og[7]);
-                gp[6] = v;
-                float4* cp = a.c_all + row * 4 + half * 2;       // 4 float4 per (t,cta,u)
+                gp[6 * kH] = v;
+                float4* cp = a.c_all + blk * (4 * kH) + half * (2 * kH) + u;
                 cp[0] = make_float4(c[0], c[1], c[2], c[3]);
-                cp[1] = make_float4(c[4], c[5], c[6], c[7]);
+                cp[kH] = make_float4(c[4], c[5], c[6], c[7]);
                 if (more) {
                     // h_t is the recurrent input of step t+1: row I+u, columns (t+1)*B + b0 + bb ..
                     __nv_bfloat16* dst = a.xh_t + static_cast<size_t>(a.I + u) * a.ld_xht +
@@ -268,7 +290,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
     __syncthreads();
     if (warp == 8) {
         tc_fence_after_sync();
-        tmem_dealloc<64>(tmem);
+        tmem_dealloc<512>(tmem);
     }
 }
 
@@ -289,8 +311,7 @@ struct LstmBwdArgs {
 __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint8_t* sA = smem;
-    uint8_t* sB = smem + kBwdASmem;
+    uint8_t* sB = smem;
     __shared__ __align__(8) uint64_t dg_ready, mma_done;
     __shared__ uint32_t tmem_slot;
 
@@ -298,40 +319,50 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     const int b0 = blockIdx.x * kNB;
 
     if (tid == 0) {
-        mbar_init(&dg_ready, kPW);
+        mbar_init(&dg_ready, kPW / 32);
         mbar_init(&mma_done, 1);
         fence_mbar_init();
     }
-    if (warp == 8) tmem_alloc<32>(&tmem_slot);
-    {
-        // Wh = kernel rows I..I+H, each 4H = 512 bf16 = 64 chunks of 16 bytes
-        const int total = kH * 64;
-        for (int idx = tid; idx < total; idx += kLstmThreads) {
-            const int r = idx >> 6, c = idx & 63;
-            cp_async_16(sA + swz_off(kH, r, c * 8), a.w + static_cast<size_t>(a.I + r) * a.ld_w + c * 8);
-        }
-    }
-    cp_async_wait_all();
-    fence_proxy_async_smem();
+    if (warp == 8) tmem_alloc<512>(&tmem_slot);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem = tmem_slot;
+    if (warp < 8) {
+        // Wh = kernel rows I..I+H (4H = 512 bf16 each) -> TMEM columns [kBwdW, kBwdW+256);
+        // thread (u, half) loads K elements [256*half, 256*half+256) of row I+u
+        const int u = static_cast<int>(tid & 127), half = static_cast<int>(tid >> 7);
+        const uint32_t lane_base = tmem + (((warp & 3u) * 32u) << 16);
+        const __nv_bfloat16* row = a.w + static_cast<size_t>(a.I + u) * a.ld_w + half * 256;
+#pragma unroll 1
+        for (int c16 = 0; c16 < 8; ++c16) {
+            uint32_t r[16];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const uint4 v = *reinterpret_cast<const uint4*>(row + c16 * 32 + q * 8);
+                r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
+            }
+            tmem_st_32x16(lane_base + kBwdW + half * 128 + c16 * 16, r);
+        }
+        tmem_st_wait();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
 
     if (warp == 8) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
-            const uint32_t a_base = smem_u32(sA), b_base = smem_u32(sB);
+            const uint32_t b_base = smem_u32(sB);
+            uint64_t db[32];
+#pragma unroll
+            for (int ks = 0; ks < 32; ++ks) db[ks] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
             for (int s = 0; s < a.T - 1; ++s) {     // no dh needed below t = 0
                 mbar_wait(&dg_ready, s & 1);
                 tc_fence_after_sync();
-#pragma unroll 4
-                for (int ks = 0; ks < 32; ++ks) {
-                    const int kb = ks >> 2, k4 = ks & 3;
-                    const uint64_t da = umma_desc_k128(a_base + kb * (kH * 128)) + 2 * k4;
-                    const uint64_t db = umma_desc_k128(b_base + kb * (kNB * 128)) + 2 * k4;
-                    umma_bf16(tmem, da, db, idesc, ks != 0 ? 1u : 0u);
-                }
+#pragma unroll
+                for (int ks = 0; ks < 32; ++ks)
+                    umma_bf16_ts(tmem, tmem + kBwdW + ks * 8, db[ks], idesc, ks != 0 ? 1u : 0u);
                 umma_commit(&mma_done);
             }
         }
@@ -341,7 +372,6 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         const int bb = half * kHB;
         const uint32_t t_lane = tmem + (((warp & 3u) * 32u) << 16) + bb;
         const bool full = (b0 + kNB <= a.B);
-        const size_t blob_row = static_cast<size_t>(gridDim.x) * kH;
         float dh[kHB], dc[kHB], c_new[kHB], c_old[kHB];
         float dbs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -352,15 +382,17 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         // saved activations of the last step
         uint4 gq[4];
         {
-            const size_t row = static_cast<size_t>(a.T - 1) * blob_row + static_cast<size_t>(blockIdx.x) * kH + u;
+            const size_t blk = static_cast<size_t>(a.T - 1) * gridDim.x + blockIdx.x;
+            const uint4* gp = a.gates + blk * (8 * kH) + half * kH + u;
 #pragma unroll
-            for (int g = 0; g < 4; ++g) gq[g] = a.gates[row * 8 + 2 * g + half];
-            const float4 c0 = a.c_all[row * 4 + half * 2], c1 = a.c_all[row * 4 + half * 2 + 1];
+            for (int g = 0; g < 4; ++g) gq[g] = gp[g * 2 * kH];
+            const float4* cp = a.c_all + blk * (4 * kH) + half * (2 * kH) + u;
+            const float4 c0 = cp[0], c1 = cp[kH];
             c_new[0] = c0.x; c_new[1] = c0.y; c_new[2] = c0.z; c_new[3] = c0.w;
             c_new[4] = c1.x; c_new[5] = c1.y; c_new[6] = c1.z; c_new[7] = c1.w;
             if (a.T > 1) {
-                const size_t rowp = row - blob_row;
-                const float4 p0 = a.c_all[rowp * 4 + half * 2], p1 = a.c_all[rowp * 4 + half * 2 + 1];
+                const float4* pp = cp - static_cast<size_t>(gridDim.x) * (4 * kH);
+                const float4 p0 = pp[0], p1 = pp[kH];
                 c_old[0] = p0.x; c_old[1] = p0.y; c_old[2] = p0.z; c_old[3] = p0.w;
                 c_old[4] = p1.x; c_old[5] = p1.y; c_old[6] = p1.z; c_old[7] = p1.w;
             } else {
@@ -407,7 +439,8 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                 }
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
-                mbar_arrive(&dg_ready);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&dg_ready);
             }
             // gate gradients for the weight-gradient GEMM: row g*H+u, 8 consecutive columns
             if (a.dg_t != nullptr) {
@@ -428,14 +461,15 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
             }
             if (t > 0) {
                 // prefetch the saved activations of step t-1 while the MMA runs
-                const size_t row = static_cast<size_t>(t - 1) * blob_row + static_cast<size_t>(blockIdx.x) * kH + u;
+                const size_t blk = static_cast<size_t>(t - 1) * gridDim.x + blockIdx.x;
+                const uint4* gp = a.gates + blk * (8 * kH) + half * kH + u;
 #pragma unroll
-                for (int g = 0; g < 4; ++g) gq[g] = a.gates[row * 8 + 2 * g + half];
+                for (int g = 0; g < 4; ++g) gq[g] = gp[g * 2 * kH];
 #pragma unroll
                 for (int b = 0; b < kHB; ++b) c_new[b] = c_old[b];
                 if (t > 1) {
-                    const size_t rowp = row - blob_row;
-                    const float4 p0 = a.c_all[rowp * 4 + half * 2], p1 = a.c_all[rowp * 4 + half * 2 + 1];
+                    const float4* pp = a.c_all + (blk - gridDim.x) * (4 * kH) + half * (2 * kH) + u;
+                    const float4 p0 = pp[0], p1 = pp[kH];
                     c_old[0] = p0.x; c_old[1] = p0.y; c_old[2] = p0.z; c_old[3] = p0.w;
                     c_old[4] = p1.x; c_old[5] = p1.y; c_old[6] = p1.z; c_old[7] = p1.w;
                 } else {
@@ -470,7 +504,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     __syncthreads();
     if (warp == 8) {
         tc_fence_after_sync();
-        tmem_dealloc<32>(tmem);
+        tmem_dealloc<512>(tmem);
     }
     if (a.dbias != nullptr) {
         // the last CTA to get here adds the per-CTA partials in CTA order
@@ -497,7 +531,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
 }  // namespace psb
 
 extern "C" size_t psb_lstm_saved_bytes(int B, int T, int H, int which) {
-    // which: 0 = gates blob, 1 = c blob
+    // which: 0 = gates blob (8 uint4 per (t, cta, unit)), 1 = c blob (4 float4 per (t, cta, unit))
     const size_t ctas = (static_cast<size_t>(B) + psb::kNB - 1) / psb::kNB;
     const size_t rows = static_cast<size_t>(T) * ctas * static_cast<size_t>(H);
     return which == 0 ? rows * 8 * 16 : rows * 4 * 16;
@@ -511,7 +545,8 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
     if (H != kH) return fail(PSB_ERR_ARG, "psb_lstm_fwd: this kernel is built for H=128 (got %d)", H);
     if (I < 1 || I > 32) return fail(PSB_ERR_ARG, "psb_lstm_fwd: input width must be 1..32 (got %d)", I);
     if (!x || !wt || !bias || B < 1 || T < 1) return fail(PSB_ERR_ARG, "psb_lstm_fwd: bad argument");
-    if (ld_wt % 8 || ld_wt < I + H) return fail(PSB_ERR_ARG, "psb_lstm_fwd: ld_wt must be a multiple of 8 covering I+H");
+    if (ld_wt % 8 || ld_wt < I + H || ld_wt > kFwdKMax)
+        return fail(PSB_ERR_ARG, "psb_lstm_fwd: ld_wt must be a multiple of 8 with I+H <= ld_wt <= 160");
     if ((gates != nullptr) != (c_all != nullptr) || (gates != nullptr) != (xh_t != nullptr))
         return fail(PSB_ERR_ARG, "psb_lstm_fwd: gates, c_all and xh_t must be given together");
     if (xh_t && (ld_xht % 8 || B % 8)) return fail(PSB_ERR_ARG, "psb_lstm_fwd: saving needs B%%8==0 and ld_xht%%8==0");
@@ -524,7 +559,7 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
     a.h_last_t = static_cast<__nv_bfloat16*>(h_last_t); a.ld_ht = ld_ht;
     a.gates = static_cast<uint4*>(gates); a.c_all = reinterpret_cast<float4*>(c_all);
     a.xh_t = static_cast<__nv_bfloat16*>(xh_t); a.ld_xht = ld_xht;
-    const size_t smem = kFwdASmem + kFwdBSmem + 1024;
+    const size_t smem = kFwdBSmem + 1024;
     static bool attr = false;
     if (!attr) {
         PSB_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -548,7 +583,7 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     a.gates = static_cast<const uint4*>(gates); a.c_all = reinterpret_cast<const float4*>(c_all);
     a.B = B; a.T = T; a.I = I;
     a.dg_t = static_cast<__nv_bfloat16*>(dg_t); a.ld_dgt = ld_dgt; a.dbias = dbias; a.dbias_part = dbias_scratch;
-    const size_t smem = kBwdASmem + kBwdBSmem + 1024;
+    const size_t smem = kBwdBSmem + 1024;
     static bool attr = false;
     if (!attr) {
         PSB_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -149,7 +149,7 @@ class LstmSaved:
         L.psb_lstm_saved_bytes.restype = ctypes.c_size_t
         L.psb_lstm_saved_bytes.argtypes = [c_int, c_int, c_int, c_int]
         self.ctas = (B + 15) // 16
-        # opaque blobs in the kernels' private layout: [t][cta][unit][gate][16] / [t][cta][unit][16]
+        # opaque blobs in the kernels' private layout (see csrc/lstm.cu)
         self.gates = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 0) // 2, dtype=torch.bfloat16, device=device)
         self.c_all = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 1) // 4, dtype=torch.float32, device=device)
         self.xh_t = BMat(I + H, T * B, device)       # [I+H, T*B]
@@ -158,12 +158,14 @@ class LstmSaved:
 
     def gates_tbh(self) -> torch.Tensor:
         """Activated gates as ``[T, 4, B, H]`` (debug/tests)."""
-        g = self.gates.view(self.T, self.ctas, self.H, 4, 16).permute(0, 3, 1, 4, 2)
+        # [t][cta][g][half][u][8] -> [t][g][cta*16 + half*8 + j][u]
+        g = self.gates.view(self.T, self.ctas, 4, 2, self.H, 8).permute(0, 2, 1, 3, 5, 4)
         return g.reshape(self.T, 4, self.ctas * 16, self.H)[:, :, : self.B]
 
     def c_tbh(self) -> torch.Tensor:
         """Cell state after every step as ``[T, B, H]`` (debug/tests)."""
-        c = self.c_all.view(self.T, self.ctas, self.H, 16).permute(0, 1, 3, 2)
+        # [t][cta][half][2][u][4] -> [t][cta*16 + half*8 + q*4 + j][u]
+        c = self.c_all.view(self.T, self.ctas, 2, 2, self.H, 4).permute(0, 1, 2, 3, 5, 4)
         return c.reshape(self.T, self.ctas * 16, self.H)[:, : self.B]
 
 

@@ -88,8 +88,8 @@ int psb_gemm_bf16_pull(const void* A, int lda, const void* B_peer, int ldb, int 
  * psb_lstm_saved_bytes, consumed by psb_lstm_bwd) and xh_t bf16 [I+H, ld_xht] whose
  * column t*B+b holds [x_t, h_{t-1}] of batch row b (the weight-gradient GEMM's A operand).
  * ref: rnn.BasicLSTMCell(128, forget_bias=1.0) + rnn.static_rnn, lstm:50-52. */
-/* Bytes of the saved-activation blobs: which = 0 gates (bf16, [t][cta][unit][gate][16]),
- * which = 1 cell state (fp32, [t][cta][unit][16]); cta = 16 batch rows. */
+/* Bytes of the saved-activation blobs: which = 0 activated gates (bf16), which = 1 cell state
+ * (fp32); private layouts documented in csrc/lstm.cu, one block per 16 batch rows. */
 size_t psb_lstm_saved_bytes(int B, int T, int H, int which);
 int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const float* bias, float forget_bias,
                  int B, int T, int I, int H, void* h_last, int ld_h, void* h_last_t, int ld_ht,
