@@ -223,7 +223,9 @@ def run_psb200(args):
     if rank == 0:
         sampler.start()
     l0 = _lib.launch_count()
+    tr.store.push_profile(reset=True)
     ms = timed_device_steps(dev_step, args.steps, world, flush)
+    push_prof = tr.store.push_profile(reset=True)
     launches = _lib.launch_count() - l0
     if tr.graph is not None:
         launches = tr.launches_per_step() * args.steps      # graph replays do not pass through the launcher
@@ -256,6 +258,7 @@ def run_psb200(args):
                     "h2d_bytes_per_step": tr.h2d_bytes_per_step(batches[0]),
                     "d2h_bytes_per_step": tr.d2h_bytes_per_step()},
             "gpu_launches": int(launches),
+            "push_pull_us_per_step": {k: round(v, 2) for k, v in push_prof.items() if k != "calls"},
             "final": {"global_step": gstep, "losses": {k: v for k, v in last.items() if k != "global_step"}},
         }
     tr.close()

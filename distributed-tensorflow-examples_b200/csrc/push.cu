@@ -52,19 +52,27 @@ struct PushArgs {
     int step_delta;
     int async_sgd_atomic;              // 1: SGD segments use atomicAdd on master (peer atomics)
     int signal_params;                 // 1: publish params-ready to peers at the end
+    unsigned long long* prof;          // optional [8]: t0, t1, -, -, sum(wait grads), sum(apply), sum(wait params), calls
 };
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// L2-coherent (L1-bypassing) 128-bit load; no "memory" clobber so independent loads can be
+// batched — ordering against the flag wait comes from the __syncthreads() after it.
 __device__ __forceinline__ float4 ld_volatile_v4(const float* p) {
     float4 r;
-    asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+    asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
                  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-                 : "l"(p)
-                 : "memory");
+                 : "l"(p));
     return r;
 }
 __device__ __forceinline__ float ld_volatile_f32(const float* p) {
     float r;
-    asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
     return r;
 }
 
@@ -73,23 +81,18 @@ struct OptCtx {
     float lr, h1, h2, eps, lr_t;
 };
 
-__device__ __forceinline__ float apply_one(const OptCtx& o, float w, float g, float* s0, float* s1, size_t i) {
+// One element of the TF dense Apply* kernels on register values; slots are updated in place.
+__device__ __forceinline__ float apply_val(const OptCtx& o, float w, float g, float& s0, float& s1) {
     if (o.kind < 0) return w;                 // refresh the compute copies only
     if (o.kind == 0) return w - o.lr * g;
     if (o.kind == 1) {
-        float ms = s0[i], mom = s1[i];
-        ms = o.h1 * ms + (1.0f - o.h1) * g * g;
-        mom = o.h2 * mom + o.lr * g * rsqrtf(ms + o.eps);
-        s0[i] = ms;
-        s1[i] = mom;
-        return w - mom;
+        s0 = o.h1 * s0 + (1.0f - o.h1) * g * g;
+        s1 = o.h2 * s1 + o.lr * g * rsqrtf(s0 + o.eps);
+        return w - s1;
     }
-    float m = s0[i], v = s1[i];
-    m += (1.0f - o.h1) * (g - m);
-    v += (1.0f - o.h2) * (g * g - v);
-    s0[i] = m;
-    s1[i] = v;
-    return w - o.lr_t * m / (sqrtf(v) + o.eps);
+    s0 += (1.0f - o.h1) * (g - s0);
+    s1 += (1.0f - o.h2) * (g * g - s1);
+    return w - o.lr_t * s0 / (sqrtf(s1) + o.eps);
 }
 
 __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
@@ -99,6 +102,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
     const bool auto_step = a.step_id == 0;
     if (auto_step) a.step_id = *reinterpret_cast<volatile uint32_t*>(a.local_ctrl + 2) + 1;
 
+    if (a.prof != nullptr && first_block && tid == 0) a.prof[0] = global_ns();
     // ---------------- cross-GPU: all gradients of this step are in place
     if (a.world > 1) {
         if (first_block) {
@@ -111,6 +115,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
             }
             __syncthreads();
             if (tid == 0) {
+                if (a.prof != nullptr) a.prof[1] = global_ns();
                 __threadfence();
                 atomicExch(a.local_ctrl, a.step_id);
             }
@@ -141,65 +146,230 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                          ((reinterpret_cast<uintptr_t>(master) & 15) == 0) &&
                          !(a.async_sgd_atomic && s.opt_kind == 0);
         const int n_dst = s.bcast ? a.n_arenas : 1;
-        const uint32_t stride = gridDim.x * kPushThreads;
-        if (vec) {
-            for (uint32_t i4 = blockIdx.x * kPushThreads + tid; i4 < s.numel / 4; i4 += stride) {
-                const size_t i = static_cast<size_t>(i4) * 4;
-                float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
-                for (int r = 0; r < a.world; ++r) {
-                    const float4 t = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
-                    g.x += t.x; g.y += t.y; g.z += t.z; g.w += t.w;
-                }
-                g.x *= a.inv_replicas; g.y *= a.inv_replicas; g.z *= a.inv_replicas; g.w *= a.inv_replicas;
-                float4 w = *reinterpret_cast<float4*>(master + i);
-                w.x = apply_one(o, w.x, g.x, s0, s1, i);
-                w.y = apply_one(o, w.y, g.y, s0, s1, i + 1);
-                w.z = apply_one(o, w.z, g.z, s0, s1, i + 2);
-                w.w = apply_one(o, w.w, g.w, s0, s1, i + 3);
-                *reinterpret_cast<float4*>(master + i) = w;
-                const int row = static_cast<int>(i / cols), col = static_cast<int>(i % cols);
-                const __nv_bfloat162 lo = __floats2bfloat162_rn(w.x, w.y), hi = __floats2bfloat162_rn(w.z, w.w);
-                for (int d = 0; d < n_dst; ++d) {
-                    __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
-                    if (s.w_off >= 0) {
-                        __nv_bfloat16* p = arena + s.w_off + static_cast<size_t>(row) * s.ld_w + col;
-                        uint2 pk;
-                        pk.x = *reinterpret_cast<const uint32_t*>(&lo);
-                        pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-                        *reinterpret_cast<uint2*>(p) = pk;
+        if (s.w_off >= 0 || s.wt_off >= 0) {
+            // ---- matrices: 32x32 tiles so that BOTH bf16 copies are written in full 32-byte
+            // sectors (the transposed copy goes through a shared-memory transpose).  Two tiles
+            // per iteration: all loads, then the math, then the stores.
+            __shared__ __nv_bfloat16 tile[2][32][34];
+            const int rows = static_cast<int>(s.numel / s.cols);
+            const int tcols = (cols + 31) >> 5, trows = (rows + 31) >> 5;
+            const int ntiles = tcols * trows;
+            const int ty = tid >> 3, tx4 = (tid & 7) * 4;
+            const bool atomic_sgd = a.async_sgd_atomic && o.kind == 0;
+            const bool v4 = (cols % 4 == 0) && (s.grad_offset % 4 == 0) && ((reinterpret_cast<uintptr_t>(master) & 15) == 0);
+            for (int t0 = blockIdx.x * 2; t0 < ntiles; t0 += gridDim.x * 2) {
+                float g[2][4], w[2][4], v0[2][4], v1[2][4];
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int tI = t0 + u;
+                    const int r = (tI / tcols) * 32 + ty, c = (tI % tcols) * 32 + tx4;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) g[u][e] = w[u][e] = v0[u][e] = v1[u][e] = 0.0f;
+                    if (tI < ntiles && r < rows && c < cols) {
+                        const size_t i = static_cast<size_t>(r) * cols + c;
+                        if (v4) {
+                            for (int rk = 0; rk < a.world; ++rk) {
+                                const float4 t = ld_volatile_v4(a.grad_ptrs[rk] + s.grad_offset + i);
+                                g[u][0] += t.x; g[u][1] += t.y; g[u][2] += t.z; g[u][3] += t.w;
+                            }
+                            if (!atomic_sgd) {
+                                const float4 t = *reinterpret_cast<const float4*>(master + i);
+                                w[u][0] = t.x; w[u][1] = t.y; w[u][2] = t.z; w[u][3] = t.w;
+                            }
+                            if (o.kind > 0) {
+                                const float4 p0 = *reinterpret_cast<const float4*>(s0 + i);
+                                const float4 p1 = *reinterpret_cast<const float4*>(s1 + i);
+                                v0[u][0] = p0.x; v0[u][1] = p0.y; v0[u][2] = p0.z; v0[u][3] = p0.w;
+                                v1[u][0] = p1.x; v1[u][1] = p1.y; v1[u][2] = p1.z; v1[u][3] = p1.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                if (c + e < cols) {
+                                    for (int rk = 0; rk < a.world; ++rk) g[u][e] += ld_volatile_f32(a.grad_ptrs[rk] + s.grad_offset + i + e);
+                                    if (!atomic_sgd) w[u][e] = master[i + e];
+                                    if (o.kind > 0) { v0[u][e] = s0[i + e]; v1[u][e] = s1[i + e]; }
+                                }
+                            }
+                        }
                     }
-                    if (s.f_off >= 0)
-                        *reinterpret_cast<float4*>(a.farena_ptrs[s.bcast ? d : s.home] + s.f_off + i) = w;
-                    if (s.wt_off >= 0) {
-                        __nv_bfloat16* p = arena + s.wt_off + static_cast<size_t>(col) * s.ld_wt + row;
-                        p[0] = lo.x;
-                        p[s.ld_wt] = lo.y;
-                        p[2 * static_cast<size_t>(s.ld_wt)] = hi.x;
-                        p[3 * static_cast<size_t>(s.ld_wt)] = hi.y;
+                }
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int tI = t0 + u;
+                    const int r = (tI / tcols) * 32 + ty, c = (tI % tcols) * 32 + tx4;
+                    const bool live = tI < ntiles && r < rows && c < cols;
+                    if (live) {
+                        const size_t i = static_cast<size_t>(r) * cols + c;
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float gg = g[u][e] * a.inv_replicas;
+                            if (c + e < cols) {
+                                if (atomic_sgd) w[u][e] = atomicAdd(master + i + e, -o.lr * gg) - o.lr * gg;
+                                else w[u][e] = apply_val(o, w[u][e], gg, v0[u][e], v1[u][e]);
+                            }
+                        }
+                        if (v4) {
+                            if (!atomic_sgd) *reinterpret_cast<float4*>(master + i) = make_float4(w[u][0], w[u][1], w[u][2], w[u][3]);
+                            if (o.kind > 0) {
+                                *reinterpret_cast<float4*>(s0 + i) = make_float4(v0[u][0], v0[u][1], v0[u][2], v0[u][3]);
+                                *reinterpret_cast<float4*>(s1 + i) = make_float4(v1[u][0], v1[u][1], v1[u][2], v1[u][3]);
+                            }
+                        } else {
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                if (c + e < cols) {
+                                    if (!atomic_sgd) master[i + e] = w[u][e];
+                                    if (o.kind > 0) { s0[i + e] = v0[u][e]; s1[i + e] = v1[u][e]; }
+                                }
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) tile[u][ty][tx4 + e] = __float2bfloat16_rn(live && c + e < cols ? w[u][e] : 0.0f);
+                    if (live && s.w_off >= 0) {
+                        const uint32_t lo = pack_bf16(w[u][0], w[u][1]), hi = pack_bf16(w[u][2], w[u][3]);
+                        for (int d = 0; d < n_dst; ++d) {
+                            __nv_bfloat16* p = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]) + s.w_off +
+                                               static_cast<size_t>(r) * s.ld_w + c;
+                            if (c + 3 < cols) {
+                                *reinterpret_cast<uint2*>(p) = make_uint2(lo, hi);
+                            } else {
+                                for (int e = 0; e < 4 && c + e < cols; ++e) p[e] = __float2bfloat16_rn(w[u][e]);
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+                if (s.wt_off >= 0) {
+#pragma unroll
+                    for (int u = 0; u < 2; ++u) {
+                        const int tI = t0 + u;
+                        // thread (cc = ty, rr4 = tx4): column cc of the tile, rows rr4..rr4+3 -> 8 contiguous bytes of wt
+                        const int cg = (tI % tcols) * 32 + ty, rg = (tI / tcols) * 32 + tx4;
+                        if (tI < ntiles && cg < cols && rg < rows) {
+                            const __nv_bfloat16 b0 = tile[u][tx4][ty], b1 = tile[u][tx4 + 1][ty], b2 = tile[u][tx4 + 2][ty],
+                                                b3 = tile[u][tx4 + 3][ty];
+                            for (int d = 0; d < n_dst; ++d) {
+                                __nv_bfloat16* p = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]) + s.wt_off +
+                                                   static_cast<size_t>(cg) * s.ld_wt + rg;
+                                if (rg + 3 < rows) {
+                                    uint2 pk;
+                                    pk.x = static_cast<uint32_t>(__bfloat16_as_ushort(b0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b1)) << 16);
+                                    pk.y = static_cast<uint32_t>(__bfloat16_as_ushort(b2)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b3)) << 16);
+                                    *reinterpret_cast<uint2*>(p) = pk;
+                                } else {
+                                    p[0] = b0;
+                                    if (rg + 1 < rows) p[1] = b1;
+                                    if (rg + 2 < rows) p[2] = b2;
+                                }
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        } else {
+        constexpr int U = 4;      // independent vectors per thread per iteration: all loads, then math, then stores
+        if (vec) {
+            const uint32_t n4 = s.numel / 4;
+            for (uint32_t base = blockIdx.x * (kPushThreads * U); base < n4; base += gridDim.x * (kPushThreads * U)) {
+                float4 g[U], w[U], v0[U], v1[U];
+#pragma unroll
+                for (int j = 0; j < U; ++j) {
+                    const uint32_t i4 = base + j * kPushThreads + tid;
+                    g[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    w[j] = v0[j] = v1[j] = g[j];
+                    if (i4 < n4) {
+                        const size_t i = static_cast<size_t>(i4) * 4;
+                        for (int r = 0; r < a.world; ++r) {
+                            const float4 t = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
+                            g[j].x += t.x; g[j].y += t.y; g[j].z += t.z; g[j].w += t.w;
+                        }
+                        w[j] = *reinterpret_cast<const float4*>(master + i);
+                        if (o.kind > 0) {
+                            v0[j] = *reinterpret_cast<const float4*>(s0 + i);
+                            v1[j] = *reinterpret_cast<const float4*>(s1 + i);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < U; ++j) {
+                    const uint32_t i4 = base + j * kPushThreads + tid;
+                    if (i4 >= n4) continue;
+                    const size_t i = static_cast<size_t>(i4) * 4;
+                    const float sc = a.inv_replicas;
+                    w[j].x = apply_val(o, w[j].x, g[j].x * sc, v0[j].x, v1[j].x);
+                    w[j].y = apply_val(o, w[j].y, g[j].y * sc, v0[j].y, v1[j].y);
+                    w[j].z = apply_val(o, w[j].z, g[j].z * sc, v0[j].z, v1[j].z);
+                    w[j].w = apply_val(o, w[j].w, g[j].w * sc, v0[j].w, v1[j].w);
+                    *reinterpret_cast<float4*>(master + i) = w[j];
+                    if (o.kind > 0) {
+                        *reinterpret_cast<float4*>(s0 + i) = v0[j];
+                        *reinterpret_cast<float4*>(s1 + i) = v1[j];
+                    }
+                    const int row = static_cast<int>(i / cols), col = static_cast<int>(i % cols);
+                    const __nv_bfloat162 lo = __floats2bfloat162_rn(w[j].x, w[j].y), hi = __floats2bfloat162_rn(w[j].z, w[j].w);
+                    for (int d = 0; d < n_dst; ++d) {
+                        __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
+                        if (s.w_off >= 0) {
+                            __nv_bfloat16* p = arena + s.w_off + static_cast<size_t>(row) * s.ld_w + col;
+                            uint2 pk;
+                            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
+                            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
+                            *reinterpret_cast<uint2*>(p) = pk;
+                        }
+                        if (s.f_off >= 0)
+                            *reinterpret_cast<float4*>(a.farena_ptrs[s.bcast ? d : s.home] + s.f_off + i) = w[j];
+                        if (s.wt_off >= 0) {
+                            __nv_bfloat16* p = arena + s.wt_off + static_cast<size_t>(col) * s.ld_wt + row;
+                            p[0] = lo.x;
+                            p[s.ld_wt] = lo.y;
+                            p[2 * static_cast<size_t>(s.ld_wt)] = hi.x;
+                            p[3 * static_cast<size_t>(s.ld_wt)] = hi.y;
+                        }
                     }
                 }
             }
         } else {
-            for (uint32_t i = blockIdx.x * kPushThreads + tid; i < s.numel; i += stride) {
-                float g = 0.0f;
-                for (int r = 0; r < a.world; ++r) g += ld_volatile_f32(a.grad_ptrs[r] + s.grad_offset + i);
-                g *= a.inv_replicas;
-                float w;
-                if (a.async_sgd_atomic && o.kind == 0) {
-                    w = atomicAdd(master + i, -o.lr * g) - o.lr * g;
-                } else {
-                    w = apply_one(o, master[i], g, s0, s1, i);
-                    master[i] = w;
+            constexpr int US = 8;
+            for (uint32_t base = blockIdx.x * (kPushThreads * US); base < s.numel; base += gridDim.x * (kPushThreads * US)) {
+                float g[US], w[US], v0[US], v1[US];
+                const bool atomic_sgd = a.async_sgd_atomic && o.kind == 0;
+#pragma unroll
+                for (int j = 0; j < US; ++j) {
+                    const uint32_t i = base + j * kPushThreads + tid;
+                    g[j] = w[j] = v0[j] = v1[j] = 0.0f;
+                    if (i < s.numel) {
+                        for (int r = 0; r < a.world; ++r) g[j] += ld_volatile_f32(a.grad_ptrs[r] + s.grad_offset + i);
+                        if (!atomic_sgd) w[j] = master[i];
+                        if (o.kind > 0) { v0[j] = s0[i]; v1[j] = s1[i]; }
+                    }
                 }
-                const int row = static_cast<int>(i / cols), col = static_cast<int>(i % cols);
-                const __nv_bfloat16 wb = __float2bfloat16_rn(w);
-                for (int d = 0; d < n_dst; ++d) {
-                    __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
-                    if (s.w_off >= 0) arena[s.w_off + static_cast<size_t>(row) * s.ld_w + col] = wb;
-                    if (s.f_off >= 0) a.farena_ptrs[s.bcast ? d : s.home][s.f_off + i] = w;
-                    if (s.wt_off >= 0) arena[s.wt_off + static_cast<size_t>(col) * s.ld_wt + row] = wb;
+#pragma unroll
+                for (int j = 0; j < US; ++j) {
+                    const uint32_t i = base + j * kPushThreads + tid;
+                    if (i >= s.numel) continue;
+                    const float gg = g[j] * a.inv_replicas;
+                    float wn;
+                    if (atomic_sgd) {
+                        wn = atomicAdd(master + i, -o.lr * gg) - o.lr * gg;
+                    } else {
+                        wn = apply_val(o, w[j], gg, v0[j], v1[j]);
+                        master[i] = wn;
+                        if (o.kind > 0) { s0[i] = v0[j]; s1[i] = v1[j]; }
+                    }
+                    const int row = static_cast<int>(i / cols), col = static_cast<int>(i % cols);
+                    const __nv_bfloat16 wb = __float2bfloat16_rn(wn);
+                    for (int d = 0; d < n_dst; ++d) {
+                        __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
+                        if (s.w_off >= 0) arena[s.w_off + static_cast<size_t>(row) * s.ld_w + col] = wb;
+                        if (s.f_off >= 0) a.farena_ptrs[s.bcast ? d : s.home][s.f_off + i] = wn;
+                        if (s.wt_off >= 0) arena[s.wt_off + static_cast<size_t>(col) * s.ld_wt + row] = wb;
+                    }
                 }
             }
+        }
         }
     }
 
@@ -212,8 +382,10 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
         is_last = (prev == total_blocks - 1);
     }
     __syncthreads();
+    unsigned long long t_applied = 0;
     if (is_last) {
         if (tid == 0) {
+            if (a.prof != nullptr) t_applied = global_ns();
             a.local_ctrl[1] = 0;
             if (auto_step) a.local_ctrl[2] = a.step_id;
             for (int k = 0; k < a.nbeta; ++k) {
@@ -230,6 +402,18 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
             // this step's parameters (they may be writing into OUR arena).
             const uint32_t* mine = a.pad_ptrs[a.rank] + kPadParams + tid;
             while (static_cast<int32_t>(ld_acquire_sys(mine) - a.step_id) < 0) {
+            }
+        }
+        if (a.prof != nullptr) {
+            __syncthreads();
+            if (tid == 0) {
+                const unsigned long long t_end = global_ns();
+                const unsigned long long t0 = *reinterpret_cast<volatile unsigned long long*>(a.prof);
+                const unsigned long long t1 = a.world > 1 ? *reinterpret_cast<volatile unsigned long long*>(a.prof + 1) : t0;
+                a.prof[4] += t1 - t0;
+                a.prof[5] += t_applied - t1;
+                a.prof[6] += t_end - t_applied;
+                a.prof[7] += 1;
             }
         }
     }
@@ -262,10 +446,12 @@ extern "C" int psb_push_apply(const psb_push_desc_t* d, void* stream) {
     a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
     a.global_step = d->global_step; a.step_delta = d->step_delta;
     a.async_sgd_atomic = d->async_sgd_atomic; a.signal_params = d->signal_params;
+    a.prof = reinterpret_cast<unsigned long long*>(d->prof);
     int gx = d->blocks_per_seg > 0 ? d->blocks_per_seg : 16;
     if (gx > 64) gx = 64;
     dim3 grid(gx, d->nseg > 0 ? d->nseg : 1);
-    if (grid.x * grid.y > 148) return fail(PSB_ERR_LIMIT, "psb_push_apply: grid %u x %u would not be co-resident", grid.x, grid.y);
+    if (d->world > 1 && grid.x * grid.y > 148)
+        return fail(PSB_ERR_LIMIT, "psb_push_apply: grid %u x %u would not be co-resident", grid.x, grid.y);
     push_apply_kernel<<<grid, kPushThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
     return after_launch("push_apply");
 }
@@ -391,6 +577,7 @@ extern "C" int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
     a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
     a.global_step = d->global_step; a.step_delta = d->step_delta;
     a.async_sgd_atomic = d->async_sgd_atomic; a.signal_params = d->signal_params;
+    a.prof = reinterpret_cast<unsigned long long*>(d->prof);
     push_apply_kernel<<<grid, kPushThreads, 0, st>>>(a);
     return after_launch("push_apply_noalloc");
 }

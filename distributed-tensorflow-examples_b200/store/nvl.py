@@ -49,7 +49,7 @@ class PushDesc(Structure):
                 ("n_arenas", c_int), ("inv_replicas", c_float), ("step_id", c_uint32),
                 ("local_ctrl", c_void_p), ("beta", BetaUpdate * 2), ("nbeta", c_int),
                 ("global_step", c_void_p), ("step_delta", c_int), ("async_sgd_atomic", c_int),
-                ("signal_params", c_int), ("blocks_per_seg", c_int)]
+                ("signal_params", c_int), ("blocks_per_seg", c_int), ("prof", c_void_p)]
 
 
 _lib.register_signature("psb_push_apply", [POINTER(PushDesc), c_void_p])
@@ -87,6 +87,7 @@ class NvlStore:
         self.grads = h.tensor(self._grad_off, (self._grad_elems,), torch.float32)
         self.global_step_t = h.tensor(self._gs_off, (1,), torch.int32)
         self.gs_owner = model.global_step.ps_task % world
+        self.prof = torch.zeros(8, dtype=torch.int64, device=self.device)
         self._tables()
         self._seg_cache = {}
         self._segs_refresh = self._build_segs(owned_only=True, peer_state=False, kind_override=-1)
@@ -309,7 +310,8 @@ class NvlStore:
         d.n_arenas = self.world
         d.local_ctrl = self.ctrl.data_ptr()
         d.step_id = 0
-        d.blocks_per_seg = 16
+        d.blocks_per_seg = max(1, min(64, 148 // max(1, nseg))) if (sync and self.world > 1) else 48
+        d.prof = self.prof.data_ptr()
         if sync:
             d.grad_ptrs, d.world, d.rank = self._t_grads.data_ptr(), self.world, self.rank
             d.inv_replicas = 1.0 / self.world
@@ -360,6 +362,20 @@ class NvlStore:
         d = self._desc(segs, n, True, 0, False)
         _lib.check(_lib.lib().psb_push_apply(ctypes.byref(d), _lib.current_stream_ptr()), "psb_push_apply(refresh)")
         torch.cuda.synchronize()
+
+    def push_profile(self, reset: bool = True) -> Dict[str, float]:
+        """Average microseconds per push spent (a) waiting for every rank's gradients, (b)
+        reducing + applying + storing the copies, (c) waiting for every owner's parameters —
+        measured inside the kernel with %globaltimer.  (a)+(c) is the exposed synchronisation
+        cost of the step, (b) the exposed push/pull work."""
+        torch.cuda.synchronize()
+        p = self.prof.cpu().tolist()
+        n = max(1, p[7])
+        out = {"calls": p[7], "wait_grads_us": p[4] / n / 1e3, "apply_us": p[5] / n / 1e3,
+               "wait_params_us": p[6] / n / 1e3}
+        if reset:
+            self.prof.zero_()
+        return out
 
     def zero_grads(self) -> None:
         self.grads.zero_()

@@ -180,6 +180,9 @@ typedef struct psb_push_desc {
     int async_sgd_atomic;
     int signal_params;               /* publish (and wait for) params-ready on the pads */
     int blocks_per_seg;              /* 0 = default */
+    uint64_t* prof;                  /* optional DEVICE [8] u64, zeroed by the caller: the kernel adds the
+                                        nanoseconds it spent waiting for gradients [4], reducing+applying [5],
+                                        waiting for parameters [6], and the call count [7] (globaltimer) */
 } psb_push_desc_t;
 
 /* Reduce-scatter + optimizer apply (+ all-gather of the bf16 copies) in one kernel over peer
