@@ -448,9 +448,10 @@ extern "C" int psb_push_apply(const psb_push_desc_t* d, void* stream) {
     a.async_sgd_atomic = d->async_sgd_atomic; a.signal_params = d->signal_params;
     a.prof = reinterpret_cast<unsigned long long*>(d->prof);
     int gx = d->blocks_per_seg > 0 ? d->blocks_per_seg : 16;
-    if (gx > 64) gx = 64;
+    if (gx > 296) gx = 296;
     dim3 grid(gx, d->nseg > 0 ? d->nseg : 1);
-    if (d->world > 1 && grid.x * grid.y > 148)
+    // the blocks spin on each other: all of them must be resident (2 x 256 threads per SM fit easily)
+    if (d->world > 1 && grid.x * grid.y > 296)
         return fail(PSB_ERR_LIMIT, "psb_push_apply: grid %u x %u would not be co-resident", grid.x, grid.y);
     push_apply_kernel<<<grid, kPushThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
     return after_launch("push_apply");

@@ -310,7 +310,9 @@ class NvlStore:
         d.n_arenas = self.world
         d.local_ctrl = self.ctrl.data_ptr()
         d.step_id = 0
-        d.blocks_per_seg = max(1, min(64, 148 // max(1, nseg))) if (sync and self.world > 1) else 48
+        big = self._grad_elems > (4 << 20)          # large shards: two CTAs per SM to keep NVLink loads in flight
+        cap = 296 if big else 148
+        d.blocks_per_seg = max(1, min(cap, cap // max(1, nseg))) if (sync and self.world > 1) else (cap // max(1, nseg) if big else 48)
         d.prof = self.prof.data_ptr()
         if sync:
             d.grad_ptrs, d.world, d.rank = self._t_grads.data_ptr(), self.world, self.rank
