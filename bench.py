@@ -31,10 +31,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-PER_GPU_BATCH = {"lstm": 128, "gan": 128, "encoder": 256}
+PER_GPU_BATCH = {"lstm": 128, "gan": 128, "encoder": 256, "scaled_lstm": 64}
 MODEL_LABEL = {"lstm": "distributed_lstm BasicLSTM(128) on 28x28 rows + linear-10, SGD 1e-3",
                "gan": "distributed_gan G 100-256-784 / D 784-256-1, 2x Adam 2e-4",
-               "encoder": "distributed_encoder 784-256-128-256-784, RMSProp 0.01"}
+               "encoder": "distributed_encoder 784-256-128-256-784, RMSProp 0.01",
+               "scaled_lstm": "scaled 2-layer LSTM hidden 4096 seq 512 bf16, SGD"}
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -128,14 +129,18 @@ def _barrier(world: int):
     torch.cuda.synchronize()
 
 
-def synthetic_batches(model: str, batch: int, n: int, seed: int):
+def synthetic_batches(model: str, batch: int, n: int, seed: int, dims=None):
     """MNIST-shaped synthetic data in pinned host memory (images in [0,1], one-hot labels)."""
     import torch
     g = torch.Generator().manual_seed(seed)
     out = []
     for _ in range(n):
         b = {}
-        if model == "lstm":
+        if model == "scaled_lstm":
+            T, I = dims["timesteps"], dims["num_input"]
+            b["x"] = torch.rand(T, batch, I, generator=g).pin_memory()
+            b["y"] = torch.nn.functional.one_hot(torch.randint(0, 10, (batch,), generator=g), 10).float().pin_memory()
+        elif model == "lstm":
             b["x"] = torch.rand(batch, 28, 28, generator=g).pin_memory()
             b["y"] = torch.nn.functional.one_hot(torch.randint(0, 10, (batch,), generator=g), 10).float().pin_memory()
         elif model == "gan":
@@ -196,14 +201,17 @@ def run_psb200(args):
     from psb200.parallel.trainer import DeviceTrainer
     rank, world, local, group = _dist_setup(args.gpus)
     model = args.model
-    B = PER_GPU_BATCH[model]
+    B = args.batch or PER_GPU_BATCH[model]
     kw = {}
     if model == "gan":
         kw["device_noise"] = False      # z is fed from the host like np.random.uniform at gan:189
-    tr = DeviceTrainer(model, rank, world, group, mode=args.mode, seed=args.seed,
-                       gan_update=args.gan_update, plan_kwargs=kw)
+    dims = None
+    if model == "scaled_lstm":
+        dims = dict(num_input=args.hidden, timesteps=args.seq, num_hidden=args.hidden, num_layers=args.layers)
+    tr = DeviceTrainer(model, rank, world, group, mode=args.mode, seed=args.seed, batch=B,
+                       gan_update=args.gan_update, plan_kwargs=kw, model_kwargs=dims)
     tr.initialize()
-    batches = synthetic_batches(model, B, 8, args.seed * 1000 + rank)
+    batches = synthetic_batches(model, B, 2 if model == "scaled_lstm" else 8, args.seed * 1000 + rank, dims)
     dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -248,7 +256,8 @@ def run_psb200(args):
             "vs_baseline": round(value / base, 3) if base else None,
             "dtype": "bf16", "data": "synthetic MNIST-shaped, random-init weights",
             "impl": "psb200",
-            "config": {"model": MODEL_LABEL[model], "global_batch": B * world, "seq_len": 28 if model == "lstm" else None,
+            "config": {"model": MODEL_LABEL[model] if dims is None else "scaled %d-layer LSTM hidden %d seq %d bf16, SGD" % (args.layers, args.hidden, args.seq),
+                       "global_batch": B * world, "seq_len": 28 if model == "lstm" else (args.seq if dims else None),
                        "parallelism": "dp%d ps-sharded (%s)" % (world, args.mode),
                        "l2": "flushed between timed iterations (256 MiB write outside the event pairs)",
                        "cuda_graph": tr.graph is not None,
@@ -298,7 +307,11 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
-    ap.add_argument("--model", default="lstm", choices=["lstm", "gan", "encoder"])
+    ap.add_argument("--model", default="lstm", choices=["lstm", "gan", "encoder", "scaled_lstm"])
+    ap.add_argument("--hidden", type=int, default=4096, help="scaled_lstm: hidden and input width")
+    ap.add_argument("--seq", type=int, default=512, help="scaled_lstm: timesteps")
+    ap.add_argument("--layers", type=int, default=2, help="scaled_lstm: stacked layers")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the model's reference value)")
     ap.add_argument("--mode", default="sync", choices=["sync", "async"])
     ap.add_argument("--gan_update", default="simultaneous", choices=["simultaneous", "alternating"])
     ap.add_argument("--impl", default="psb200", choices=["psb200", "reference", "torch_ddp"])

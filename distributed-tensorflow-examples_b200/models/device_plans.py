@@ -230,6 +230,118 @@ class LstmPlan(DevicePlan):
         return 7
 
 
+class ScaledLstmPlan(DevicePlan):
+    """Stacked large-H LSTM: per layer one big GEMM for the input projections of all timesteps,
+    then per timestep a full-chip GEMM ``h_{t-1} Wh`` + the pointwise cell kernel; backward mirrors
+    it and batches both weight gradients and the gradient to the layer below into large GEMMs.
+    Input ``x`` is time-major fp32 ``[T, B, I]``."""
+
+    def __init__(self, model, store, batch=None):
+        super().__init__(model, store, batch or model.batch_size)
+        B, dev = self.B, self.dev
+        T, I, H, L, C = model.T, model.I, model.H, model.L, model.C
+        TB = T * B
+        self.inputs["x"] = torch.zeros(T, B, I, device=dev)
+        self.inputs["y"] = torch.zeros(B, C, device=dev)
+        self.X0, self.X0T = BMat(TB, I, dev), BMat(I, TB, dev)
+        self.Hall = [BMat(TB, H, dev) for _ in range(L)]             # h_t of every step (time-major rows)
+        self.HprevT = BMat(H, TB, dev)                               # [h_{t-1}]^T, reused per layer
+        self.XinT = BMat(H, TB, dev) if L > 1 else None              # layer input transposed (layers >= 1)
+        self.gx = torch.zeros(TB, 4 * H, device=dev)                 # x-part pre-activations (reused per layer)
+        self.gh = torch.zeros(B, 4 * H, device=dev)
+        self.gates = [torch.zeros(TB, 4 * H, dtype=torch.bfloat16, device=dev) for _ in range(L)]
+        self.c_all = [torch.zeros(TB, H, device=dev) for _ in range(L)]
+        self.c = torch.zeros(B, H, device=dev)
+        self.h0 = BMat(B, H, dev)                                    # zero initial state
+        self.dG, self.dGT = BMat(TB, 4 * H, dev), BMat(4 * H, TB, dev)
+        self.dh_rec = torch.zeros(B, H, device=dev)
+        self.dc = torch.zeros(B, H, device=dev)
+        self.dY = torch.zeros(TB, H, device=dev) if L > 1 else None  # gradient arriving from the layer above
+        self.logits = torch.zeros(B, C, device=dev)
+        self.losses["loss"] = torch.zeros((), device=dev)
+        self.correct = torch.zeros((), device=dev)
+        self.dlogits, self.dlogits_t = BMat(B, C, dev), BMat(C, B, dev)
+        self.dh_top = torch.zeros(B, H, device=dev)
+        self.h_last_t = BMat(H, B, dev)
+
+    def _rows(self, m: BMat, t: int) -> BMat:
+        return m.rows_view(t * self.B, (t + 1) * self.B)
+
+    def forward(self, train: bool = True) -> None:
+        s, n, mdl, B = self.store, self._name, self.model, self.B
+        T, H = mdl.T, mdl.H
+        K.cast_transpose(self.inputs["x"].view(T * B, mdl.I), self.X0, self.X0T if train else None)
+        inp = self.X0
+        for l in range(mdl.L):
+            I = mdl.in_dim(l)
+            wt = s.wt_src(n("kernel%d" % l))                  # [4H, I+H]
+            wx_t, wh_t = wt.cols_view(0, I), wt.cols_view(I, I + H)
+            bias = s.vec_src(n("bias%d" % l))
+            K.gemm(inp, wx_t, out_f32=self.gx)                # all timesteps at once
+            self.c.zero_()
+            for t in range(T):
+                hprev = self.h0 if t == 0 else self._rows(self.Hall[l], t - 1)
+                K.gemm(hprev, wh_t, out_f32=self.gh)
+                K.lstm_cell_fwd(self.gx[t * B:(t + 1) * B], self.gh, bias, 1.0, self.c, self._rows(self.Hall[l], t),
+                                self.gates[l][t * B:(t + 1) * B] if train else None,
+                                self.c_all[l][t * B:(t + 1) * B] if train else None)
+            inp = self.Hall[l]
+        h_last = self._rows(self.Hall[-1], T - 1)
+        K.gemm(h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits)
+
+    def forward_backward(self) -> None:
+        s, n, mdl, B = self.store, self._name, self.model, self.B
+        T, H = mdl.T, mdl.H
+        TB = T * B
+        s.zero_grads()
+        self.forward(train=True)
+        K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits, self.dlogits_t,
+                            s.grad(n("out_b")), self.correct)
+        h_last = self._rows(self.Hall[-1], T - 1)
+        K.transpose_bf16(h_last, self.h_last_t)
+        K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
+        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh_top)
+        for l in range(mdl.L - 1, -1, -1):
+            I = mdl.in_dim(l)
+            w = s.w_src(n("kernel%d" % l))                    # [I+H, 4H]
+            wx, wh = w.rows_view(0, I), w.rows_view(I, I + H)
+            gk = s.grad(n("kernel%d" % l))
+            self.dc.zero_()
+            top = l == mdl.L - 1
+            for t in range(T - 1, -1, -1):
+                dy = None
+                if top:
+                    dy = self.dh_top if t == T - 1 else None
+                else:
+                    dy = self.dY[t * B:(t + 1) * B]
+                K.lstm_cell_bwd(self.dh_rec if t < T - 1 else None, dy, self.gates[l][t * B:(t + 1) * B],
+                                self.c_all[l][t * B:(t + 1) * B],
+                                self.c_all[l][(t - 1) * B:t * B] if t > 0 else None, self.dc,
+                                self._rows(self.dG, t), s.grad(n("bias%d" % l)))
+                if t > 0:
+                    K.gemm(self._rows(self.dG, t), wh, out_f32=self.dh_rec)
+            # weight gradients of this layer in two large GEMMs over all (t, b)
+            K.transpose_bf16(self.dG, self.dGT)
+            # [h_{t-1}]^T: column block t holds h_{t-1}; block 0 is the zero state
+            self.HprevT.t[:, :B].zero_()
+            if T > 1:
+                K.transpose_bf16(self.Hall[l].rows_view(0, (T - 1) * B), self.HprevT.cols_view(B, TB))
+            K.gemm(self.HprevT, self.dGT, out_f32=gk[I:])
+            if l == 0:
+                K.gemm(self.X0T, self.dGT, out_f32=gk[:I])
+            else:
+                K.transpose_bf16(self.Hall[l - 1], self.XinT)
+                K.gemm(self.XinT, self.dGT, out_f32=gk[:I])
+                K.gemm(self.dG, wx, out_f32=self.dY)          # gradient to the layer below, all timesteps
+
+    def evaluate(self) -> None:
+        self.forward(train=False)
+        K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], None, None, None, self.correct)
+
+    def kernels_per_step(self) -> int:
+        return self.model.L * self.model.T * 4 + 20
+
+
 def make_plan(model, store: NvlStore, batch: Optional[int] = None, **kw) -> DevicePlan:
-    cls = {"encoder": EncoderPlan, "gan": GanPlan, "lstm": LstmPlan}[model.name]
+    cls = {"encoder": EncoderPlan, "gan": GanPlan, "lstm": LstmPlan, "scaled_lstm": ScaledLstmPlan}[model.name]
     return cls(model, store, batch or model.batch_size, **kw)

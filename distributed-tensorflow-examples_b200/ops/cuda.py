@@ -250,3 +250,36 @@ def uniform_noise(rows: int, cols: int, lo: float, hi: float, seed: int,
         _ptr(out), rows, cols, out.stride(0) if out is not None else 0, lo, hi, seed & 0xFFFFFFFF,
         _ptr(step_counter), _ptr(out_bf16), out_bf16.ld if out_bf16 is not None else 0,
         _ptr(out_t), out_t.ld if out_t is not None else 0, current_stream_ptr()), "psb_uniform_noise")
+
+
+# --------------------------------------------------------------------------- large-H LSTM path
+_lib.register_signature("psb_lstm_cell_fwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_float, c_void_p,
+                                              c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p])
+_lib.register_signature("psb_lstm_cell_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+                                              c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p])
+_lib.register_signature("psb_transpose_bf16", [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p])
+
+
+def lstm_cell_fwd(gx: torch.Tensor, gh: torch.Tensor, bias: torch.Tensor, forget_bias: float,
+                  c: torch.Tensor, h_out: BMat, gates_save: Optional[torch.Tensor] = None,
+                  c_save: Optional[torch.Tensor] = None) -> None:
+    B, H = c.shape
+    check(_lib.lib().psb_lstm_cell_fwd(gx.data_ptr(), gx.stride(0), gh.data_ptr(), gh.stride(0),
+                                       bias.data_ptr(), float(forget_bias), c.data_ptr(), h_out.ptr, h_out.ld,
+                                       _ptr(gates_save), _ptr(c_save), B, H, current_stream_ptr()),
+          "psb_lstm_cell_fwd")
+
+
+def lstm_cell_bwd(dh_rec: Optional[torch.Tensor], dy: Optional[torch.Tensor], gates: torch.Tensor,
+                  c_new: torch.Tensor, c_prev: Optional[torch.Tensor], dc: torch.Tensor, dg: BMat,
+                  dbias: Optional[torch.Tensor]) -> None:
+    B, H = dc.shape
+    check(_lib.lib().psb_lstm_cell_bwd(_ptr(dh_rec), dh_rec.stride(0) if dh_rec is not None else 0,
+                                       _ptr(dy), dy.stride(0) if dy is not None else 0, gates.data_ptr(),
+                                       c_new.data_ptr(), _ptr(c_prev), dc.data_ptr(), dg.ptr, dg.ld,
+                                       _ptr(dbias), B, H, current_stream_ptr()), "psb_lstm_cell_bwd")
+
+
+def transpose_bf16(src: BMat, dst: BMat) -> None:
+    check(_lib.lib().psb_transpose_bf16(src.ptr, src.ld, src.rows, src.cols, dst.ptr, dst.ld,
+                                        current_stream_ptr()), "psb_transpose_bf16")

@@ -123,19 +123,25 @@ def lstm_fwd(x: torch.Tensor, kernel: torch.Tensor, bias: torch.Tensor,
     return h, saved
 
 
-def lstm_bwd(dh_last: torch.Tensor, saved: LstmSaved, kernel: torch.Tensor
-             ) -> Tuple[torch.Tensor, torch.Tensor]:
-    """BPTT for :func:`lstm_fwd` when only the last hidden state feeds the loss.
-    Returns ``(d_kernel [I+H,4H], d_bias [4H])``."""
+def lstm_bwd(dh_last: Optional[torch.Tensor], saved: LstmSaved, kernel: torch.Tensor,
+             dh_seq: Optional[torch.Tensor] = None, need_dx: bool = False):
+    """BPTT for :func:`lstm_fwd`.  ``dh_last`` [B,H] is the gradient reaching the last hidden
+    state (the reference's case, ``outputs[-1]``); ``dh_seq`` [T,B,H] optionally adds a gradient
+    at every step (a stacked layer above).  Returns ``(d_kernel [I+H,4H], d_bias [4H])`` and,
+    with ``need_dx``, also ``d_x [B,T,I]``."""
     T, B, IH = saved.xh.shape
     H = kernel.shape[1] // 4
     I = IH - H
-    dh = dh_last
-    dc = torch.zeros_like(dh_last)
+    dh = torch.zeros(B, H, dtype=kernel.dtype, device=kernel.device) if dh_last is None else dh_last
+    dc = torch.zeros_like(dh)
     dk = torch.zeros_like(kernel)
     db = kernel.new_zeros(4 * H)
     wh_t = kernel[I:, :].t()        # [4H, H]
+    wx_t = kernel[:I, :].t()        # [4H, I]
+    dxs = []
     for t in range(T - 1, -1, -1):
+        if dh_seq is not None:
+            dh = dh + dh_seq[t]
         i, j, f, o = saved.gates[t].split(H, dim=1)
         c_new, c_old = saved.c[t + 1], saved.c[t]
         tc = torch.tanh(c_new)
@@ -146,5 +152,9 @@ def lstm_bwd(dh_last: torch.Tensor, saved: LstmSaved, kernel: torch.Tensor
         dk += saved.xh[t].t() @ dg
         db += dg.sum(0)
         dh = dg @ wh_t
+        if need_dx:
+            dxs.append(dg @ wx_t)
         dc = dc * f
+    if need_dx:
+        return dk, db, torch.stack(dxs[::-1], dim=1)
     return dk, db

@@ -28,14 +28,15 @@ from ..store.nvl import NvlStore
 class DeviceTrainer:
     def __init__(self, model_name: str, rank: int = 0, world: int = 1, group=None, mode: str = "sync",
                  batch: Optional[int] = None, seed: int = 0, use_graph: bool = True,
-                 gan_update: str = "simultaneous", bcast: bool = True, plan_kwargs: Optional[dict] = None):
+                 gan_update: str = "simultaneous", bcast: bool = True, plan_kwargs: Optional[dict] = None,
+                 model_kwargs: Optional[dict] = None):
         if not torch.cuda.is_available():
             raise RuntimeError("DeviceTrainer needs a CUDA device; the CPU path is psb200.session.Session")
         _lib.lib()   # fail loudly if the kernel library is missing
         self.rank, self.world, self.group, self.mode, self.seed = rank, world, group, mode, seed
         self.registry = VariableRegistry(replica_device_setter(
             worker_device="/job:worker/task:%d" % rank, ps_tasks=world))
-        self.model = make_model(model_name).build(self.registry)
+        self.model = make_model(model_name, **(model_kwargs or {})).build(self.registry)
         self.store = NvlStore(self.model, self.registry, rank, world, group, mode=mode, bcast=bcast)
         kw = dict(plan_kwargs or {})
         if self.model.name == "gan":

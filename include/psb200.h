@@ -106,6 +106,23 @@ int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const
                  const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
                  float* dbias, float* dbias_scratch, void* stream);
 
+/* ------------------------------------------------------------------ large-H LSTM path
+ * Pointwise halves of a BasicLSTMCell step for hidden sizes whose kernel cannot be resident on
+ * one SM (the scaled 2-layer H=4096 configuration): the gate GEMMs run through psb_gemm_bf16.
+ * Forward: pre = gx + gh + bias (fp32 [B,4H], gate order i,j,f,o), c fp32 [B,H] updated in place,
+ * h_out bf16 [B, ld_h]; optional saves for backward (activated gates bf16 [B,4H], c fp32 [B,H]).
+ * Backward: dh = dh_rec + dy (either may be NULL), dc fp32 [B,H] updated in place, dg bf16
+ * [B, ld_dg] = gate gradients, dbias fp32 [4H] += column sums (atomic).
+ * ref: rnn.BasicLSTMCell / static_rnn, lstm:50-52, scaled per BASELINE.json config #4. */
+int psb_lstm_cell_fwd(const float* gx, int ld_gx, const float* gh, int ld_gh, const float* bias,
+                      float forget_bias, float* c, void* h_out, int ld_h, void* gates_save,
+                      float* c_save, int B, int H, void* stream);
+int psb_lstm_cell_bwd(const float* dh_rec, int ld_dh, const float* dy, int ld_dy, const void* gates,
+                      const float* c_new, const float* c_prev, float* dc, void* dg, int ld_dg,
+                      float* dbias, int B, int H, void* stream);
+/* out[c][r] = in[r][c], bf16, leading dimensions in elements. */
+int psb_transpose_bf16(const void* in, int ld_in, int R, int C, void* out, int ld_out, void* stream);
+
 /* ------------------------------------------------------------------ input cast, losses
  * fp32 [M,N] -> bf16 [M, ld_out] (zero pad columns) and/or its transpose bf16 [N, ld_t].
  * ref: feed_dict of the float32 placeholders, encoder:165, gan:192-194, lstm:128. */
