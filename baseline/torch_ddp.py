@@ -40,6 +40,19 @@ class LSTMNet(nn.Module):
         return F.cross_entropy(logits.float(), y.argmax(1))
 
 
+class StackedLSTM(nn.Module):
+    """cuDNN rendition of the scaled configuration: nn.LSTM(H, H, num_layers) + linear head."""
+
+    def __init__(self, hidden=4096, layers=2):
+        super().__init__()
+        self.rnn = nn.LSTM(hidden, hidden, num_layers=layers)      # time-major input [T, B, I]
+        self.head = nn.Linear(hidden, 10)
+
+    def forward(self, x, y):
+        out, _ = self.rnn(x)
+        return F.cross_entropy(self.head(out[-1]).float(), y.argmax(1))
+
+
 class G(nn.Module):
     def __init__(self):
         super().__init__()
@@ -66,7 +79,7 @@ def _wrap(m, world, local):
     return m
 
 
-def build_step(model: str, world: int, local: int):
+def build_step(model: str, world: int, local: int, dims=None):
     """Returns (step_fn(batch) -> loss tensor, input names)."""
     if model == "encoder":
         net = _wrap(AE(), world, local)
@@ -76,6 +89,17 @@ def build_step(model: str, world: int, local: int):
             opt.zero_grad(set_to_none=True)
             with torch.autocast("cuda", dtype=torch.bfloat16):
                 loss = net(b["x"])
+            loss.backward()
+            opt.step()
+            return loss
+        return step
+    if model == "scaled_lstm":
+        net = _wrap(StackedLSTM(dims["num_hidden"], dims["num_layers"]).to(torch.bfloat16), world, local)
+        opt = torch.optim.SGD(net.parameters(), lr=0.001)
+
+        def step(b):
+            opt.zero_grad(set_to_none=True)
+            loss = net(b["x"].to(torch.bfloat16), b["y"])
             loss.backward()
             opt.step()
             return loss
@@ -131,9 +155,12 @@ def build_step(model: str, world: int, local: int):
 
 def run(args, rank, world, local, bench):
     model = args.model
-    B = bench.PER_GPU_BATCH[model]
-    step = build_step(model, world, local)
-    batches = bench.synthetic_batches(model, B, 8, args.seed * 1000 + rank)
+    B = args.batch or bench.PER_GPU_BATCH[model]
+    dims = None
+    if model == "scaled_lstm":
+        dims = dict(num_input=args.hidden, timesteps=args.seq, num_hidden=args.hidden, num_layers=args.layers)
+    step = build_step(model, world, local, dims)
+    batches = bench.synthetic_batches(model, B, 2 if dims else 8, args.seed * 1000 + rank, dims)
     dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     host_loss = torch.zeros(1).pin_memory()

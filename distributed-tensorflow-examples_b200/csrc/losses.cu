@@ -64,16 +64,37 @@ __global__ void __launch_bounds__(256) mse_sigmoid_grad_kernel(const float* __re
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const float inv = 1.0f / (static_cast<float>(M) * static_cast<float>(N));
     float part = 0.0f, csum = 0.0f;
-    for (int m0 = 0; m0 < M; m0 += 32) {
+    // software pipeline: the loads of row-tile k+1 are in flight while tile k is processed
+    float yn[4], xn[4];
+    const int n = n0 + tx;
 #pragma unroll
-        for (int r = ty; r < 32; r += 8) {
-            const int m = m0 + r, n = n0 + tx;
+    for (int q = 0; q < 4; ++q) {
+        const int m = ty + 8 * q;
+        const bool ok = m < M && n < N;
+        yn[q] = ok ? y[static_cast<size_t>(m) * ld_y + n] : 0.0f;
+        xn[q] = ok ? x[static_cast<size_t>(m) * ld_x + n] : 0.0f;
+    }
+    for (int m0 = 0; m0 < M; m0 += 32) {
+        float yc[4], xc[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) { yc[q] = yn[q]; xc[q] = xn[q]; }
+        if (m0 + 32 < M) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int m = m0 + 32 + ty + 8 * q;
+                const bool ok = m < M && n < N;
+                yn[q] = ok ? y[static_cast<size_t>(m) * ld_y + n] : 0.0f;
+                xn[q] = ok ? x[static_cast<size_t>(m) * ld_x + n] : 0.0f;
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int r = ty + 8 * q, m = m0 + r;
             float g = 0.0f;
             if (m < M && n < N) {
-                const float yv = y[static_cast<size_t>(m) * ld_y + n];
-                const float d = yv - x[static_cast<size_t>(m) * ld_x + n];
+                const float d = yc[q] - xc[q];
                 part += d * d;
-                g = 2.0f * d * inv * yv * (1.0f - yv);
+                g = 2.0f * d * inv * yc[q] * (1.0f - yc[q]);
             }
             tile[r][tx] = g;
             if (dz != nullptr && m < M && n < ld_dz) dz[static_cast<size_t>(m) * ld_dz + n] = __float2bfloat16_rn(g);
@@ -81,8 +102,8 @@ __global__ void __launch_bounds__(256) mse_sigmoid_grad_kernel(const float* __re
         __syncthreads();
 #pragma unroll
         for (int r = ty; r < 32; r += 8) {
-            const int n = n0 + r, m = m0 + tx;
-            if (dz_t != nullptr && n < N && m < M) dz_t[static_cast<size_t>(n) * ld_dzt + m] = __float2bfloat16_rn(tile[tx][r]);
+            const int nn = n0 + r, m = m0 + tx;
+            if (dz_t != nullptr && nn < N && m < M) dz_t[static_cast<size_t>(nn) * ld_dzt + m] = __float2bfloat16_rn(tile[tx][r]);
         }
         if (ty == 0) {
 #pragma unroll

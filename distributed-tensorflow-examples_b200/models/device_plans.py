@@ -36,6 +36,16 @@ class DevicePlan:
         self.dev = store.device
         self.inputs = {}
         self.losses = {}
+        # independent branches of the backward pass (weight gradients vs. the dgrad chain) are
+        # issued on a side stream; inside the captured graph they become parallel branches
+        self.side = torch.cuda.Stream(device=self.dev)
+
+    def _fork(self) -> None:
+        """Side stream may start once everything issued so far on the main stream is done."""
+        self.side.wait_stream(torch.cuda.current_stream())
+
+    def _join(self) -> None:
+        torch.cuda.current_stream().wait_stream(self.side)
 
     def _name(self, key: str) -> str:
         return self.model.var[key].name
@@ -88,11 +98,14 @@ class EncoderPlan(DevicePlan):
         K.mse_sigmoid_grad(self.y, self.inputs["x"], self.losses["loss"], self.dz[4], self.dz_t[4],
                            s.grad(n(self.bkeys[3])))
         for l in range(3, -1, -1):
-            # dW_l = act_{l}^T dz_{l+1}
-            K.gemm(self.act_t[l], self.dz_t[l + 1], out_f32=s.grad(n(self.wkeys[l])))
+            # dW_l = act_{l}^T dz_{l+1}  (side stream: only the dgrad chain is on the critical path)
+            self._fork()
+            with torch.cuda.stream(self.side):
+                K.gemm(self.act_t[l], self.dz_t[l + 1], out_f32=s.grad(n(self.wkeys[l])))
             if l > 0:
                 K.gemm(self.dz[l + 1], s.w_src(n(self.wkeys[l])), yprev=self.act[l], dact=1,
                        out=self.dz[l], out_t=self.dz_t[l], colsum=s.grad(n(self.bkeys[l - 1])))
+        self._join()
 
     def kernels_per_step(self) -> int:
         return 1 + 4 + 1 + 4 + 3
@@ -152,10 +165,13 @@ class GanPlan(DevicePlan):
         K.gan_loss_grad(self.logit, B, self.losses_t, self.d_disc, self.d_disc_t, self.d_gen,
                         s.grad(n("b_disc_out")) if disc else None)
         if disc:
-            K.gemm(self.DHT, self.d_disc_t, out_f32=s.grad(n("w_disc_out")))
-            K.gemm(self.d_disc, s.w_src(n("w_disc_out")), yprev=self.DH, dact=2, out=self.dZ1, out_t=self.dZ1T,
-                   colsum=s.grad(n("b_disc_hidden1")))
-            K.gemm(self.DinT, self.dZ1T, out_f32=s.grad(n("w_disc_hidden1")))
+            # discriminator-variable path on the side stream, generator-variable path on the main one
+            self._fork()
+            with torch.cuda.stream(self.side):
+                K.gemm(self.DHT, self.d_disc_t, out_f32=s.grad(n("w_disc_out")))
+                K.gemm(self.d_disc, s.w_src(n("w_disc_out")), yprev=self.DH, dact=2, out=self.dZ1, out_t=self.dZ1T,
+                       colsum=s.grad(n("b_disc_hidden1")))
+                K.gemm(self.DinT, self.dZ1T, out_f32=s.grad(n("w_disc_hidden1")))
         if gen:
             K.gemm(self.d_gen, s.w_src(n("w_disc_out")), yprev=self.DH_fake, dact=2, out=self.dZ1f)
             K.gemm(self.dZ1f, s.w_src(n("w_disc_hidden1")), yprev=self.Din_fake, dact=1, out=self.dZo,
@@ -164,6 +180,8 @@ class GanPlan(DevicePlan):
             K.gemm(self.dZo, s.w_src(n("w_gen_out")), yprev=self.GH, dact=2, out=self.dZh, out_t=self.dZhT,
                    colsum=s.grad(n("b_gen_hidden1")))
             K.gemm(self.ZT, self.dZhT, out_f32=s.grad(n("w_gen_hidden1")))
+        if disc:
+            self._join()
 
     def kernels_per_step(self) -> int:
         return 2 + 4 + 1 + 3 + 5
@@ -221,10 +239,13 @@ class LstmPlan(DevicePlan):
         self.forward(train=True)
         K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
                             self.dlogits_t, s.grad(n("out_b")), self.correct)
-        K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
+        self._fork()
+        with torch.cuda.stream(self.side):
+            K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
         K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh)
         K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
         K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")))
+        self._join()
 
     def kernels_per_step(self) -> int:
         return 7
