@@ -35,15 +35,24 @@ constexpr int kH = 128;              // hidden units (UMMA M of one gate block)
 constexpr int kNB = 16;              // batch rows per CTA (UMMA N)
 constexpr int kHB = 8;               // batch rows per pointwise thread
 constexpr int kPW = 256;             // pointwise threads (8 warps)
-constexpr int kLstmThreads = kPW + 32;   // + 1 MMA warp
+constexpr int kMmaWarps = 4;           // backward: issuing warps (a thread sustains ~1 tcgen05.mma / 50 cycles)
+constexpr int kLstmThreads = kPW + 32 * kMmaWarps;
+constexpr int kFwdMmaWarps = 4;        // forward: one issuing warp per gate block
+constexpr int kFwdThreads = kPW + 32 * kFwdMmaWarps;
 constexpr int kFwdKB = 3;            // k-blocks of 64 covering I+H <= 160 (+pad)
 constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144: the [x_t, h_{t-1}] operand
 constexpr int kFwdKMax = 160;        // I + H <= 160: 80 TMEM columns per gate block
-constexpr uint32_t kFwdAcc = 0;      // TMEM columns [0, 64): gate accumulators
-constexpr uint32_t kFwdW = 64;       // TMEM columns [64, 64 + 4*80): the cell kernel (A operand)
+// One thread sustains about one tcgen05.mma per ~50 cycles (measured with clock64 around the
+// issue loop), so the k-steps are spread over several issuing warps: one per gate block here,
+// four interleaved accumulators in the backward kernel.
+constexpr uint32_t kFwdAcc = 0;      // TMEM columns [0, 64): gate accumulators (columns 64..127 unused)
+constexpr uint32_t kFwdW = 128;      // TMEM columns [128, 128 + 4*80): the cell kernel (A operand)
 constexpr int kBwdKB = 8;            // 4H / 64
 constexpr int kBwdBSmem = kBwdKB * kNB * 128;      // 16384: the dG_t operand
-constexpr uint32_t kBwdW = 32;       // TMEM columns [32, 32 + 256): Wh (A operand); [0,16): dh accumulator
+constexpr int kStageRow = 144;                 // 128 data bytes + 16 pad: conflict-free 16-byte column writes
+constexpr int kFwdStage = kH * kStageRow;      // h rows x (4 steps x 16 batch) bf16, double-buffered
+constexpr int kBwdStage = 4 * kH * kStageRow;  // dG rows x (4 steps x 16 batch) bf16, double-buffered
+constexpr uint32_t kBwdW = 64;       // TMEM columns [64, 64 + 256): Wh (A operand); [0,64): four partial dh accumulators
 
 __device__ __forceinline__ float sigmoid_t(float x) { return fmaf(0.5f, fast_tanh(0.5f * x), 0.5f); }
 
@@ -56,6 +65,28 @@ __device__ __forceinline__ uint32_t swz_off(int rows, int row, int k) {
 
 __device__ __forceinline__ void sts_bf16(uint8_t* base, uint32_t off, uint32_t packed_lo16) {
     *reinterpret_cast<uint16_t*>(base + off) = static_cast<uint16_t>(packed_lo16);
+}
+
+
+// Column order shared by xh_t and dg_t (the two operands of the weight-gradient GEMM):
+//   col(cta, t, b) = (cta * T + t) * 16 + b
+// so that four consecutive timesteps of one CTA are 128 contiguous bytes of a row.  The kernels
+// stage four steps in shared memory and flush them as full 128-byte lines.
+__device__ __forceinline__ void flush_group(const uint8_t* stage, int nrows, __nv_bfloat16* dst, int ld,
+                                            size_t col0, int valid_slots, uint32_t pw_warp, uint32_t lane) {
+    const int per_warp = nrows / 8;                       // 8 pointwise warps; 4 rows per warp-instruction
+    const int ch = static_cast<int>(lane) & 7;
+    if ((ch >> 1) >= valid_slots) return;
+    const int r0 = static_cast<int>(pw_warp) * per_warp + (static_cast<int>(lane) >> 3);
+#pragma unroll 4
+    for (int k = 0; k < per_warp; k += 16) {
+        uint4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) v[j] = *reinterpret_cast<const uint4*>(stage + (r0 + k + 4 * j) * kStageRow + ch * 16);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(dst + static_cast<size_t>(r0 + k + 4 * j) * ld + col0 + ch * 8) = v[j];
+    }
 }
 
 struct LstmFwdArgs {
@@ -76,10 +107,11 @@ struct LstmFwdArgs {
     int ld_xht;
 };
 
-__global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a) {
+__global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sB = smem;
+    uint8_t* sStage = smem + kFwdBSmem;                  // 2 x kFwdStage
     __shared__ __align__(8) uint64_t xh_ready, mma_done;
     __shared__ uint32_t tmem_slot;
 
@@ -89,12 +121,12 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
 
     if (tid == 0) {
         mbar_init(&xh_ready, kPW / 32);       // one arrival per pointwise warp
-        mbar_init(&mma_done, 1);
+        mbar_init(&mma_done, kFwdMmaWarps);   // one tcgen05.commit per issuing warp
         fence_mbar_init();
     }
     if (warp == 8) tmem_alloc<512>(&tmem_slot);
-    for (int idx = tid; idx < kFwdBSmem / 16; idx += kLstmThreads)
-        reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);
+    for (int idx = tid; idx < (kFwdBSmem + 2 * kFwdStage) / 16; idx += blockDim.x)
+        reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);     // operand tile and h staging (h_{-1} = 0)
     tc_fence_before_sync();
     __syncthreads();   // sB zeroed before x_0 goes in; TMEM base address published
     tc_fence_after_sync();
@@ -132,7 +164,6 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
             const float xv = (b0 + b < a.B) ? a.x[(static_cast<size_t>(b0 + b) * a.T + 0) * a.I + i] : 0.0f;
             const __nv_bfloat16 xb = __float2bfloat16_rn(xv);
             *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, i)) = xb;
-            if (a.xh_t != nullptr && b0 + b < a.B) a.xh_t[static_cast<size_t>(i) * a.ld_xht + b0 + b] = xb;
         }
     }
     fence_proxy_async_smem();
@@ -140,31 +171,26 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
     __syncthreads();
     tc_fence_after_sync();
 
-    if (warp == 8) {
-        // ===================== MMA issuer =====================
+    if (warp >= 8) {
+        // ===================== MMA issuers: warp 8+g owns gate block g =====================
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
             const uint32_t b_base = smem_u32(sB);
+            const int g = static_cast<int>(warp) - 8;
             const int ksteps = (K + 15) >> 4;                    // <= 10
             uint64_t db[kFwdKMax / 16];                           // loop-invariant B descriptors
 #pragma unroll
             for (int ks = 0; ks < kFwdKMax / 16; ++ks)
                 db[ks] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
-            const uint32_t acc = tmem + kFwdAcc, wbase = tmem + kFwdW;
+            const uint32_t acc = tmem + kFwdAcc + g * kNB, wbase = tmem + kFwdW + g * (kFwdKMax / 2);
             for (int t = 0; t < a.T; ++t) {
                 if (t > 0) {
                     mbar_wait(&xh_ready, (t - 1) & 1);
                     tc_fence_after_sync();
                 }
 #pragma unroll
-                for (int ks = 0; ks < kFwdKMax / 16; ++ks) {
-                    if (ks < ksteps) {
-#pragma unroll
-                        for (int g = 0; g < 4; ++g)
-                            umma_bf16_ts(acc + g * kNB, wbase + g * (kFwdKMax / 2) + ks * 8, db[ks], idesc,
-                                         ks != 0 ? 1u : 0u);
-                    }
-                }
+                for (int ks = 0; ks < kFwdKMax / 16; ++ks)
+                    if (ks < ksteps) umma_bf16_ts(acc, wbase + ks * 8, db[ks], idesc, ks != 0 ? 1u : 0u);
                 umma_commit(&mma_done);
             }
         }
@@ -176,24 +202,36 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
         const uint32_t t_lane = tmem + (((warp & 3u) * 32u) << 16) + bb;
         const float bi = a.bias[u], bj = a.bias[kH + u], bf = a.bias[2 * kH + u] + a.forget_bias,
                     bo = a.bias[3 * kH + u];
-        const bool full = (b0 + kNB <= a.B);
         float c[kHB];
 #pragma unroll
         for (int b = 0; b < kHB; ++b) c[b] = 0.0f;
+
+        // loop-invariant addressing (no integer divisions inside the time loop)
+        uint32_t h_off[kHB];
+#pragma unroll
+        for (int b = 0; b < kHB; ++b) h_off[b] = swz_off(kNB, bb + b, a.I + u);
+        const float* xsrc[2];
+        uint32_t x_off[2];
+        bool x_ok[2];
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const int e = static_cast<int>(tid) + q * kPW;
+            const int b = e / a.I, i = e % a.I;
+            x_ok[q] = e < x_per_step;
+            x_off[q] = x_ok[q] ? swz_off(kNB, b, i) : 0u;
+            const bool in_batch = x_ok[q] && (b0 + b < a.B);
+            xsrc[q] = in_batch ? a.x + (static_cast<size_t>(b0 + b) * a.T) * a.I + i : nullptr;
+        }
+        const bool saving = a.gates != nullptr;
+        const size_t cta_col0 = static_cast<size_t>(blockIdx.x) * a.T * kNB;     // first xh_t column of this CTA
 
         for (int t = 0; t < a.T; ++t) {
             // prefetch x_{t+1} for this slice (independent of the recurrence)
             float xn[2];
             const bool more = t + 1 < a.T;
 #pragma unroll
-            for (int q = 0; q < 2; ++q) {
-                const int e = static_cast<int>(tid) + q * kPW;
-                xn[q] = 0.0f;
-                if (more && e < x_per_step) {
-                    const int b = e / a.I, i = e % a.I;
-                    if (b0 + b < a.B) xn[q] = a.x[(static_cast<size_t>(b0 + b) * a.T + (t + 1)) * a.I + i];
-                }
-            }
+            for (int q = 0; q < 2; ++q)
+                xn[q] = (more && xsrc[q] != nullptr) ? xsrc[q][static_cast<size_t>(t + 1) * a.I] : 0.0f;
             mbar_wait(&mma_done, t & 1);
             tc_fence_after_sync();
             uint32_t ri[8], rj[8], rf[8], ro[8];
@@ -217,23 +255,20 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
             hp.x = pack_bf16(h[0], h[1]); hp.y = pack_bf16(h[2], h[3]);
             hp.z = pack_bf16(h[4], h[5]); hp.w = pack_bf16(h[6], h[7]);
             if (more) {
-                // h_t -> B operand (columns I..I+H), rows bb..bb+7
+                // h_t -> B operand (columns I..I+H), rows bb..bb+7; x_{t+1} -> columns 0..I
                 const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
 #pragma unroll
                 for (int p = 0; p < 4; ++p) {
-                    sts_bf16(sB, swz_off(kNB, bb + 2 * p, a.I + u), hv[p] & 0xffffu);
-                    sts_bf16(sB, swz_off(kNB, bb + 2 * p + 1, a.I + u), hv[p] >> 16);
+                    sts_bf16(sB, h_off[2 * p], hv[p] & 0xffffu);
+                    sts_bf16(sB, h_off[2 * p + 1], hv[p] >> 16);
                 }
 #pragma unroll
-                for (int q = 0; q < 2; ++q) {
-                    const int e = static_cast<int>(tid) + q * kPW;
-                    if (e < x_per_step) {
-                        const int b = e / a.I, i = e % a.I;
-                        const __nv_bfloat16 xb = __float2bfloat16_rn(xn[q]);
-                        *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, i)) = xb;
-                        if (a.xh_t != nullptr && b0 + b < a.B)
-                            a.xh_t[static_cast<size_t>(i) * a.ld_xht + static_cast<size_t>(t + 1) * a.B + b0 + b] = xb;
-                    }
+                for (int q = 0; q < 2; ++q)
+                    if (x_ok[q]) *reinterpret_cast<__nv_bfloat16*>(sB + x_off[q]) = __float2bfloat16_rn(xn[q]);
+                if (saving) {
+                    // h_t is column block s = t+1 of xh_t: stage it (slot s&3 of buffer (s>>2)&1)
+                    const int sidx = t + 1;
+                    *reinterpret_cast<uint4*>(sStage + ((sidx >> 2) & 1) * kFwdStage + u * kStageRow + (sidx & 3) * 32 + half * 16) = hp;
                 }
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
@@ -256,20 +291,11 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
                 float4* cp = a.c_all + blk * (4 * kH) + half * (2 * kH) + u;
                 cp[0] = make_float4(c[0], c[1], c[2], c[3]);
                 cp[kH] = make_float4(c[4], c[5], c[6], c[7]);
-                if (more) {
-                    // h_t is the recurrent input of step t+1: row I+u, columns (t+1)*B + b0 + bb ..
-                    __nv_bfloat16* dst = a.xh_t + static_cast<size_t>(a.I + u) * a.ld_xht +
-                                         static_cast<size_t>(t + 1) * a.B + b0 + bb;
-                    if (full) {
-                        *reinterpret_cast<uint4*>(dst) = hp;
-                    } else {
-                        const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
-                        for (int b = 0; b < kHB && b0 + bb + b < a.B; ++b) {
-                            const uint16_t bits = static_cast<uint16_t>((b & 1) ? (hv[b >> 1] >> 16) : (hv[b >> 1] & 0xffffu));
-                            *reinterpret_cast<uint16_t*>(dst + b) = bits;
-                        }
-                    }
-                }
+                // group (t>>2) of h columns is complete and visible (every warp staged step t-1's
+                // h before arriving on xh_ready, and this step's mma_done wait ordered after that)
+                if ((t & 3) == 3)
+                    flush_group(sStage + ((t >> 2) & 1) * kFwdStage, kH, a.xh_t + static_cast<size_t>(a.I) * a.ld_xht,
+                                a.ld_xht, cta_col0 + static_cast<size_t>(t >> 2) * 64, 4, warp, lane);
             }
             if (!more) {
                 const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
@@ -292,6 +318,22 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_fwd_kernel(LstmFwdArgs a
         tc_fence_after_sync();
         tmem_dealloc<512>(tmem);
     }
+    if (warp < 8 && a.gates != nullptr && (a.T & 3) != 0) {
+        // tail: the last (partial) group of h columns, steps 4*(T>>2) .. T-1
+        const int grp = (a.T - 1) >> 2;
+        flush_group(sStage + (grp & 1) * kFwdStage, kH, a.xh_t + static_cast<size_t>(a.I) * a.ld_xht, a.ld_xht,
+                    static_cast<size_t>(blockIdx.x) * a.T * kNB + static_cast<size_t>(grp) * 64, a.T & 3, warp, lane);
+    }
+}
+
+// x rows of xh_t: out[i][(cta*T + t)*16 + bl] = bf16(x[cta*16 + bl][t][i])
+__global__ void lstm_xt_kernel(const float* __restrict__ x, int B, int T, int I, __nv_bfloat16* out, int ld) {
+    const int t = blockIdx.x, cta = blockIdx.y;
+    for (int e = threadIdx.x; e < I * kNB; e += blockDim.x) {
+        const int i = e / kNB, bl = e % kNB, b = cta * kNB + bl;
+        const float v = b < B ? x[(static_cast<size_t>(b) * T + t) * I + i] : 0.0f;
+        out[static_cast<size_t>(i) * ld + (static_cast<size_t>(cta) * T + t) * kNB + bl] = __float2bfloat16_rn(v);
+    }
 }
 
 struct LstmBwdArgs {
@@ -312,6 +354,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sB = smem;
+    uint8_t* sStage = smem + kBwdBSmem;                  // 2 x kBwdStage
     __shared__ __align__(8) uint64_t dg_ready, mma_done;
     __shared__ uint32_t tmem_slot;
 
@@ -320,7 +363,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
 
     if (tid == 0) {
         mbar_init(&dg_ready, kPW / 32);
-        mbar_init(&mma_done, 1);
+        mbar_init(&mma_done, kMmaWarps);
         fence_mbar_init();
     }
     if (warp == 8) tmem_alloc<512>(&tmem_slot);
@@ -350,19 +393,25 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     __syncthreads();
     tc_fence_after_sync();
 
-    if (warp == 8) {
+    if (warp >= 8) {
+        // a single thread sustains roughly one tcgen05.mma per ~50 cycles, so the 32 k-steps are
+        // issued by four warps, each accumulating its quarter into its own TMEM accumulator
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
             const uint32_t b_base = smem_u32(sB);
-            uint64_t db[32];
+            const int j = static_cast<int>(warp) - 8;
+            uint64_t db[8];
 #pragma unroll
-            for (int ks = 0; ks < 32; ++ks) db[ks] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
+            for (int q = 0; q < 8; ++q) {
+                const int ks = 4 * q + j;
+                db[q] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
+            }
             for (int s = 0; s < a.T - 1; ++s) {     // no dh needed below t = 0
                 mbar_wait(&dg_ready, s & 1);
                 tc_fence_after_sync();
 #pragma unroll
-                for (int ks = 0; ks < 32; ++ks)
-                    umma_bf16_ts(tmem, tmem + kBwdW + ks * 8, db[ks], idesc, ks != 0 ? 1u : 0u);
+                for (int q = 0; q < 8; ++q)
+                    umma_bf16_ts(tmem + j * kNB, tmem + kBwdW + (4 * q + j) * 8, db[q], idesc, q != 0 ? 1u : 0u);
                 umma_commit(&mma_done);
             }
         }
@@ -371,7 +420,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         const int half = static_cast<int>(tid >> 7);
         const int bb = half * kHB;
         const uint32_t t_lane = tmem + (((warp & 3u) * 32u) << 16) + bb;
-        const bool full = (b0 + kNB <= a.B);
+        const size_t cta_col0 = static_cast<size_t>(blockIdx.x) * a.T * kNB;
         float dh[kHB], dc[kHB], c_new[kHB], c_old[kHB];
         float dbs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -400,7 +449,25 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                 for (int b = 0; b < kHB; ++b) c_old[b] = 0.0f;
             }
         }
+        // loop-invariant shared-memory offsets of this thread's 8 batch rows (gate 0; +4096 per gate)
+        uint32_t row_off[kHB];
+#pragma unroll
+        for (int b = 0; b < kHB; ++b) row_off[b] = swz_off(kNB, bb + b, u);
         for (int t = a.T - 1, s = 0; t >= 0; --t, ++s) {
+            // prefetch the saved activations of step t-1 now: they have the whole step to arrive
+            uint4 gq_n[4];
+            float4 cp0 = make_float4(0.f, 0.f, 0.f, 0.f), cp1 = cp0;
+            if (t > 0) {
+                const size_t blk = static_cast<size_t>(t - 1) * gridDim.x + blockIdx.x;
+                const uint4* gp = a.gates + blk * (8 * kH) + half * kH + u;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) gq_n[g] = gp[g * 2 * kH];
+                if (t > 1) {
+                    const float4* pp = a.c_all + (blk - gridDim.x) * (4 * kH) + half * (2 * kH) + u;
+                    cp0 = pp[0];
+                    cp1 = pp[kH];
+                }
+            }
             float di[kHB], dj[kHB], df[kHB], dO[kHB];
             const uint32_t gi[4] = {gq[0].x, gq[0].y, gq[0].z, gq[0].w};
             const uint32_t gj[4] = {gq[1].x, gq[1].y, gq[1].z, gq[1].w};
@@ -426,6 +493,12 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
             pk[1].x = pack_bf16(dj[0], dj[1]); pk[1].y = pack_bf16(dj[2], dj[3]); pk[1].z = pack_bf16(dj[4], dj[5]); pk[1].w = pack_bf16(dj[6], dj[7]);
             pk[2].x = pack_bf16(df[0], df[1]); pk[2].y = pack_bf16(df[2], df[3]); pk[2].z = pack_bf16(df[4], df[5]); pk[2].w = pack_bf16(df[6], df[7]);
             pk[3].x = pack_bf16(dO[0], dO[1]); pk[3].y = pack_bf16(dO[2], dO[3]); pk[3].z = pack_bf16(dO[4], dO[5]); pk[3].w = pack_bf16(dO[6], dO[7]);
+            if (a.dg_t != nullptr) {
+                // gate gradients of step t -> staging (row g*H+u, slot t&3 of buffer (t>>2)&1)
+                uint8_t* st = sStage + ((t >> 2) & 1) * kBwdStage + (t & 3) * 32 + half * 16;
+#pragma unroll
+                for (int g = 0; g < 4; ++g) *reinterpret_cast<uint4*>(st + (g * kH + u) * kStageRow) = pk[g];
+            }
             if (t > 0) {
                 // B operand of dh_{t-1}^T = Wh * dG_t^T : element (row b, col g*H+u)
 #pragma unroll
@@ -433,8 +506,8 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                     const uint32_t v[4] = {pk[g].x, pk[g].y, pk[g].z, pk[g].w};
 #pragma unroll
                     for (int p = 0; p < 4; ++p) {
-                        sts_bf16(sB, swz_off(kNB, bb + 2 * p, g * kH + u), v[p] & 0xffffu);
-                        sts_bf16(sB, swz_off(kNB, bb + 2 * p + 1, g * kH + u), v[p] >> 16);
+                        sts_bf16(sB, row_off[2 * p] + g * (2 * kNB * 128), v[p] & 0xffffu);
+                        sts_bf16(sB, row_off[2 * p + 1] + g * (2 * kNB * 128), v[p] >> 16);
                     }
                 }
                 tc_fence_before_sync();
@@ -442,47 +515,30 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&dg_ready);
             }
-            // gate gradients for the weight-gradient GEMM: row g*H+u, 8 consecutive columns
-            if (a.dg_t != nullptr) {
-#pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    __nv_bfloat16* dst = a.dg_t + static_cast<size_t>(g * kH + u) * a.ld_dgt +
-                                         static_cast<size_t>(t) * a.B + b0 + bb;
-                    if (full) {
-                        *reinterpret_cast<uint4*>(dst) = pk[g];
-                    } else {
-                        const uint32_t v[4] = {pk[g].x, pk[g].y, pk[g].z, pk[g].w};
-                        for (int b = 0; b < kHB && b0 + bb + b < a.B; ++b) {
-                            const uint16_t bits = static_cast<uint16_t>((b & 1) ? (v[b >> 1] >> 16) : (v[b >> 1] & 0xffffu));
-                            *reinterpret_cast<uint16_t*>(dst + b) = bits;
-                        }
-                    }
-                }
-            }
+            // (the stage write below happened before the arrive; the flush of a completed group of
+            //  four timesteps is issued here, off the critical path)
+            if (a.dg_t != nullptr && t + 1 < a.T && ((t + 1) & 3) == 0)
+                flush_group(sStage + (((t + 1) >> 2) & 1) * kBwdStage, 4 * kH, a.dg_t, a.ld_dgt,
+                            cta_col0 + static_cast<size_t>((t + 1) >> 2) * 64,
+                            (a.T - (t + 1)) < 4 ? (a.T - (t + 1)) : 4, warp, lane);
             if (t > 0) {
-                // prefetch the saved activations of step t-1 while the MMA runs
-                const size_t blk = static_cast<size_t>(t - 1) * gridDim.x + blockIdx.x;
-                const uint4* gp = a.gates + blk * (8 * kH) + half * kH + u;
 #pragma unroll
-                for (int g = 0; g < 4; ++g) gq[g] = gp[g * 2 * kH];
+                for (int g = 0; g < 4; ++g) gq[g] = gq_n[g];
 #pragma unroll
                 for (int b = 0; b < kHB; ++b) c_new[b] = c_old[b];
-                if (t > 1) {
-                    const float4* pp = a.c_all + (blk - gridDim.x) * (4 * kH) + half * (2 * kH) + u;
-                    const float4 p0 = pp[0], p1 = pp[kH];
-                    c_old[0] = p0.x; c_old[1] = p0.y; c_old[2] = p0.z; c_old[3] = p0.w;
-                    c_old[4] = p1.x; c_old[5] = p1.y; c_old[6] = p1.z; c_old[7] = p1.w;
-                } else {
-#pragma unroll
-                    for (int b = 0; b < kHB; ++b) c_old[b] = 0.0f;
-                }
+                c_old[0] = cp0.x; c_old[1] = cp0.y; c_old[2] = cp0.z; c_old[3] = cp0.w;
+                c_old[4] = cp1.x; c_old[5] = cp1.y; c_old[6] = cp1.z; c_old[7] = cp1.w;
                 mbar_wait(&mma_done, s & 1);
                 tc_fence_after_sync();
-                uint32_t r[8];
-                tmem_ld_32x8(t_lane, r);
+                uint32_t r0[8], r1[8], r2[8], r3[8];
+                tmem_ld_32x8(t_lane, r0);
+                tmem_ld_32x8(t_lane + kNB, r1);
+                tmem_ld_32x8(t_lane + 2 * kNB, r2);
+                tmem_ld_32x8(t_lane + 3 * kNB, r3);
                 tmem_ld_wait();
 #pragma unroll
-                for (int b = 0; b < kHB; ++b) dh[b] = __uint_as_float(r[b]);
+                for (int b = 0; b < kHB; ++b)
+                    dh[b] = (__uint_as_float(r0[b]) + __uint_as_float(r1[b])) + (__uint_as_float(r2[b]) + __uint_as_float(r3[b]));
             }
         }
         if (a.dbias != nullptr) {
@@ -506,6 +562,11 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         tc_fence_after_sync();
         tmem_dealloc<512>(tmem);
     }
+    if (warp < 8 && a.dg_t != nullptr) {
+        // group 0 (steps 0..3) completes with the last iteration: flush it after the CTA-wide sync
+        flush_group(sStage, 4 * kH, a.dg_t, a.ld_dgt, static_cast<size_t>(blockIdx.x) * a.T * kNB,
+                    a.T < 4 ? a.T : 4, warp, lane);
+    }
     if (a.dbias != nullptr) {
         // the last CTA to get here adds the per-CTA partials in CTA order
         __shared__ bool last;
@@ -517,7 +578,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         __syncthreads();
         if (last) {
             __threadfence();
-            for (int i = tid; i < 4 * kH; i += kLstmThreads) {
+            for (int i = tid; i < 4 * kH; i += blockDim.x) {
                 float s = 0.0f;
                 for (unsigned int cta = 0; cta < gridDim.x; ++cta)
                     s += *reinterpret_cast<volatile float*>(a.dbias_part + static_cast<size_t>(cta) * 4 * kH + i);
@@ -549,7 +610,7 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
         return fail(PSB_ERR_ARG, "psb_lstm_fwd: ld_wt must be a multiple of 8 with I+H <= ld_wt <= 160");
     if ((gates != nullptr) != (c_all != nullptr) || (gates != nullptr) != (xh_t != nullptr))
         return fail(PSB_ERR_ARG, "psb_lstm_fwd: gates, c_all and xh_t must be given together");
-    if (xh_t && (ld_xht % 8 || B % 8)) return fail(PSB_ERR_ARG, "psb_lstm_fwd: saving needs B%%8==0 and ld_xht%%8==0");
+    if (xh_t && (ld_xht % 8)) return fail(PSB_ERR_ARG, "psb_lstm_fwd: saving needs ld_xht%%8==0");
     if (gates && ((reinterpret_cast<uintptr_t>(gates) | reinterpret_cast<uintptr_t>(c_all)) & 15))
         return fail(PSB_ERR_ARG, "psb_lstm_fwd: gates and c_all must be 16-byte aligned");
     LstmFwdArgs a;
@@ -559,13 +620,21 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
     a.h_last_t = static_cast<__nv_bfloat16*>(h_last_t); a.ld_ht = ld_ht;
     a.gates = static_cast<uint4*>(gates); a.c_all = reinterpret_cast<float4*>(c_all);
     a.xh_t = static_cast<__nv_bfloat16*>(xh_t); a.ld_xht = ld_xht;
-    const size_t smem = kFwdBSmem + 1024;
+    const size_t smem = kFwdBSmem + 2 * kFwdStage + 1024;
     static bool attr = false;
     if (!attr) {
         PSB_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
-    lstm_fwd_kernel<<<(B + kNB - 1) / kNB, kLstmThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    const int ctas = (B + kNB - 1) / kNB;
+    if (xh_t != nullptr) {
+        if (ld_xht < ctas * T * kNB)
+            return fail(PSB_ERR_ARG, "psb_lstm_fwd: xh_t needs %d columns (ceil(B/16)*T*16)", ctas * T * kNB);
+        lstm_xt_kernel<<<dim3(T, ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, B, T, I, a.xh_t, ld_xht);
+        int rc = after_launch("lstm_xt");
+        if (rc != PSB_OK) return rc;
+    }
+    lstm_fwd_kernel<<<ctas, kFwdThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return after_launch("lstm_fwd");
 }
 
@@ -576,14 +645,15 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     if (H != kH) return fail(PSB_ERR_ARG, "psb_lstm_bwd: this kernel is built for H=128 (got %d)", H);
     if (!w || !dh_last || !gates || !c_all || B < 1 || T < 1) return fail(PSB_ERR_ARG, "psb_lstm_bwd: bad argument");
     if (ld_w % 8 || ld_w < 4 * H) return fail(PSB_ERR_ARG, "psb_lstm_bwd: ld_w must be a multiple of 8 covering 4H");
-    if (dg_t && (ld_dgt % 8 || B % 8)) return fail(PSB_ERR_ARG, "psb_lstm_bwd: dg_t needs B%%8==0 and ld_dgt%%8==0");
+    if (dg_t && (ld_dgt % 8 || ld_dgt < ((B + kNB - 1) / kNB) * T * kNB))
+        return fail(PSB_ERR_ARG, "psb_lstm_bwd: dg_t needs ld_dgt%%8==0 and ceil(B/16)*T*16 columns");
     if (dbias && !dbias_scratch) return fail(PSB_ERR_ARG, "psb_lstm_bwd: dbias needs dbias_scratch (ceil(B/16)*4H+1 zeroed floats)");
     LstmBwdArgs a;
     a.w = static_cast<const __nv_bfloat16*>(w); a.ld_w = ld_w; a.dh_last = dh_last; a.ld_dh = ld_dh;
     a.gates = static_cast<const uint4*>(gates); a.c_all = reinterpret_cast<const float4*>(c_all);
     a.B = B; a.T = T; a.I = I;
     a.dg_t = static_cast<__nv_bfloat16*>(dg_t); a.ld_dgt = ld_dgt; a.dbias = dbias; a.dbias_part = dbias_scratch;
-    const size_t smem = kBwdBSmem + 1024;
+    const size_t smem = kBwdBSmem + 2 * kBwdStage + 1024;
     static bool attr = false;
     if (!attr) {
         PSB_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

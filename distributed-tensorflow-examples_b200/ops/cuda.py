@@ -145,15 +145,16 @@ class LstmSaved:
 
     def __init__(self, B: int, T: int, I: int, H: int, device="cuda"):
         self.B, self.T, self.I, self.H = B, T, I, H
+        self.ctas = (B + 15) // 16
         L = _lib.lib()
         L.psb_lstm_saved_bytes.restype = ctypes.c_size_t
         L.psb_lstm_saved_bytes.argtypes = [c_int, c_int, c_int, c_int]
-        self.ctas = (B + 15) // 16
         # opaque blobs in the kernels' private layout (see csrc/lstm.cu)
         self.gates = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 0) // 2, dtype=torch.bfloat16, device=device)
         self.c_all = torch.zeros(L.psb_lstm_saved_bytes(B, T, H, 1) // 4, dtype=torch.float32, device=device)
-        self.xh_t = BMat(I + H, T * B, device)       # [I+H, T*B]
-        self.dg_t = BMat(4 * H, T * B, device)       # [4H, T*B]
+        # operands of the weight-gradient GEMM; column order (cta, t, b16) — see csrc/lstm.cu
+        self.xh_t = BMat(I + H, self.ctas * T * 16, device)
+        self.dg_t = BMat(4 * H, self.ctas * T * 16, device)
         self.dbias_scratch = torch.zeros(self.ctas * 4 * H + 1, dtype=torch.float32, device=device)
 
     def gates_tbh(self) -> torch.Tensor:
@@ -161,6 +162,11 @@ class LstmSaved:
         # [t][cta][g][half][u][8] -> [t][g][cta*16 + half*8 + j][u]
         g = self.gates.view(self.T, self.ctas, 4, 2, self.H, 8).permute(0, 2, 1, 3, 5, 4)
         return g.reshape(self.T, 4, self.ctas * 16, self.H)[:, :, : self.B]
+
+    def xh_tb(self) -> torch.Tensor:
+        """``xh_t`` un-permuted to ``[I+H, T*B]`` with column ``t*B + b`` (debug/tests)."""
+        v = self.xh_t.float().view(self.I + self.H, self.ctas, self.T, 16).permute(0, 2, 1, 3)
+        return v.reshape(self.I + self.H, self.T, self.ctas * 16)[:, :, : self.B].reshape(self.I + self.H, self.T * self.B)
 
     def c_tbh(self) -> torch.Tensor:
         """Cell state after every step as ``[T, B, H]`` (debug/tests)."""

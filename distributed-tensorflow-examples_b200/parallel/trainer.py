@@ -130,6 +130,18 @@ class DeviceTrainer:
         out["global_step"] = int(self._host_step[0])
         return out
 
+    def trace_step(self) -> Dict[str, float]:
+        """One EAGER (un-graphed) step with CUDA-event timing per phase: forward+backward
+        kernels vs the fused push/pull kernel.  Milliseconds per phase."""
+        from ..utils.trace import PhaseTimer
+        with PhaseTimer() as pt:
+            with pt.phase("forward_backward"):
+                self.plan.forward_backward()
+            with pt.phase("push_pull"):
+                self.store.push()
+        self.local_step += 1
+        return pt.report()
+
     def h2d_bytes_per_step(self, batch: Dict[str, torch.Tensor]) -> int:
         return sum(v.numel() * v.element_size() for k, v in batch.items() if k in self.plan.inputs)
 

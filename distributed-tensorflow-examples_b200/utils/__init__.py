@@ -1,0 +1,5 @@
+"""Timing, tracing and clock-sampling helpers."""
+from .clocks import ClockSampler
+from .trace import PhaseTimer
+
+__all__ = ["ClockSampler", "PhaseTimer"]

@@ -85,8 +85,10 @@ int psb_gemm_bf16_pull(const void* A, int lda, const void* B_peer, int ldb, int 
  * point into a peer GPU's memory (the parameter pull is then part of this kernel).
  * Optional outputs: h_last bf16 [B, ld_h], h_last_t bf16 [H, ld_ht]; for training also the
  * two saved-activation blobs `gates` / `c_all` (opaque, 16-byte aligned, sized by
- * psb_lstm_saved_bytes, consumed by psb_lstm_bwd) and xh_t bf16 [I+H, ld_xht] whose
- * column t*B+b holds [x_t, h_{t-1}] of batch row b (the weight-gradient GEMM's A operand).
+ * psb_lstm_saved_bytes, consumed by psb_lstm_bwd) and xh_t bf16 [I+H, ld_xht], the
+ * weight-gradient GEMM's A operand: column (cta*T + t)*16 + b16 holds [x_t, h_{t-1}] of batch
+ * row cta*16 + b16, so it needs ceil(B/16)*T*16 columns (psb_lstm_bwd writes dg_t in the same
+ * column order; four consecutive timesteps of a row are one 128-byte line).
  * ref: rnn.BasicLSTMCell(128, forget_bias=1.0) + rnn.static_rnn, lstm:50-52. */
 /* Bytes of the saved-activation blobs: which = 0 activated gates (bf16), which = 1 cell state
  * (fp32); private layouts documented in csrc/lstm.cu, one block per 16 batch rows. */

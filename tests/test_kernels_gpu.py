@@ -36,7 +36,7 @@ def test_lstm_fwd_bwd(B, T, I):
     assert _rel(saved.gates_tbh().float(), gates_ref) < 3e-2
     assert _rel(saved.c_tbh(), sv.c[1:]) < 3e-2
     xh_ref = sv.xh.permute(2, 0, 1).reshape(I + H, T * B)
-    assert _rel(saved.xh_t.float(), xh_ref) < 3e-2
+    assert _rel(saved.xh_tb(), xh_ref) < 3e-2
 
     dbias = torch.zeros(4 * H, device="cuda")
     K_.lstm_bwd(W, dh_last, saved, dbias)
