@@ -40,8 +40,11 @@ constexpr int kLstmThreads = kPW + 32 * kMmaWarps;
 constexpr int kFwdMmaWarps = 4;        // forward: one issuing warp per gate block
 constexpr int kFwdThreads = kPW + 32 * kFwdMmaWarps;
 constexpr int kFwdKB = 3;            // k-blocks of 64 covering I+H <= 160 (+pad)
-constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144: the [x_t, h_{t-1}] operand
+constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144 >= 16 x 160 x 2: the [x_t, h_{t-1}] operand
 constexpr int kFwdKMax = 160;        // I + H <= 160: 80 TMEM columns per gate block
+// [x_t, h_{t-1}] operand, MN-major without swizzle: element (b, k) of the 16 x 160 tile at
+//   (b>>3)*kXhSbo + (k>>3)*128 + (k&7)*16 + (b&7)*2   — a thread's 8 batch rows of one k are 16 bytes
+constexpr uint32_t kXhSbo = (kFwdKMax / 8) * 128;
 // One thread sustains about one tcgen05.mma per ~50 cycles (measured with clock64 around the
 // issue loop), so the k-steps are spread over several issuing warps: one per gate block here,
 // four interleaved accumulators in the backward kernel.
@@ -61,6 +64,10 @@ __device__ __forceinline__ float sigmoid_t(float x) { return fmaf(0.5f, fast_tan
 __device__ __forceinline__ uint32_t swz_off(int rows, int row, int k) {
     const int kb = k >> 6, kk = k & 63;
     return static_cast<uint32_t>(kb * rows * 128 + row * 128 + ((((kk >> 3) ^ (row & 7)) << 4)) + ((kk & 7) << 1));
+}
+
+__device__ __forceinline__ uint32_t xh_off(int b, int k) {
+    return static_cast<uint32_t>((b >> 3) * kXhSbo + (k >> 3) * 128 + (k & 7) * 16 + (b & 7) * 2);
 }
 
 __device__ __forceinline__ void sts_bf16(uint8_t* base, uint32_t off, uint32_t packed_lo16) {
@@ -163,7 +170,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
             const int b = e / a.I, i = e % a.I;
             const float xv = (b0 + b < a.B) ? a.x[(static_cast<size_t>(b0 + b) * a.T + 0) * a.I + i] : 0.0f;
             const __nv_bfloat16 xb = __float2bfloat16_rn(xv);
-            *reinterpret_cast<__nv_bfloat16*>(sB + swz_off(kNB, b, i)) = xb;
+            *reinterpret_cast<__nv_bfloat16*>(sB + xh_off(b, i)) = xb;
         }
     }
     fence_proxy_async_smem();
@@ -174,14 +181,14 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
     if (warp >= 8) {
         // ===================== MMA issuers: warp 8+g owns gate block g =====================
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
+            constexpr uint32_t idesc = umma_idesc_bf16_bmn(kH, kNB);
             const uint32_t b_base = smem_u32(sB);
             const int g = static_cast<int>(warp) - 8;
             const int ksteps = (K + 15) >> 4;                    // <= 10
             uint64_t db[kFwdKMax / 16];                           // loop-invariant B descriptors
 #pragma unroll
             for (int ks = 0; ks < kFwdKMax / 16; ++ks)
-                db[ks] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
+                db[ks] = umma_desc_mn_interleaved(b_base + ks * 256, 128, kXhSbo);
             const uint32_t acc = tmem + kFwdAcc + g * kNB, wbase = tmem + kFwdW + g * (kFwdKMax / 2);
             for (int t = 0; t < a.T; ++t) {
                 if (t > 0) {
@@ -207,9 +214,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
         for (int b = 0; b < kHB; ++b) c[b] = 0.0f;
 
         // loop-invariant addressing (no integer divisions inside the time loop)
-        uint32_t h_off[kHB];
-#pragma unroll
-        for (int b = 0; b < kHB; ++b) h_off[b] = swz_off(kNB, bb + b, a.I + u);
+        const uint32_t h_off = xh_off(bb, a.I + u);           // this thread's 8 batch rows of k = I+u: 16 bytes
         const float* xsrc[2];
         uint32_t x_off[2];
         bool x_ok[2];
@@ -218,7 +223,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
             const int e = static_cast<int>(tid) + q * kPW;
             const int b = e / a.I, i = e % a.I;
             x_ok[q] = e < x_per_step;
-            x_off[q] = x_ok[q] ? swz_off(kNB, b, i) : 0u;
+            x_off[q] = x_ok[q] ? xh_off(b, i) : 0u;
             const bool in_batch = x_ok[q] && (b0 + b < a.B);
             xsrc[q] = in_batch ? a.x + (static_cast<size_t>(b0 + b) * a.T) * a.I + i : nullptr;
         }
@@ -256,12 +261,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
             hp.z = pack_bf16(h[4], h[5]); hp.w = pack_bf16(h[6], h[7]);
             if (more) {
                 // h_t -> B operand (columns I..I+H), rows bb..bb+7; x_{t+1} -> columns 0..I
-                const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
-#pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    sts_bf16(sB, h_off[2 * p], hv[p] & 0xffffu);
-                    sts_bf16(sB, h_off[2 * p + 1], hv[p] >> 16);
-                }
+                *reinterpret_cast<uint4*>(sB + h_off) = hp;
 #pragma unroll
                 for (int q = 0; q < 2; ++q)
                     if (x_ok[q]) *reinterpret_cast<__nv_bfloat16*>(sB + x_off[q]) = __float2bfloat16_rn(xn[q]);
@@ -397,14 +397,17 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         // a single thread sustains roughly one tcgen05.mma per ~50 cycles, so the 32 k-steps are
         // issued by four warps, each accumulating its quarter into its own TMEM accumulator
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(kH, kNB);
+            // dG_t is stored MN-major (the 16 batch rows of one k contiguous): element (b, k) at
+            //   (b>>3)*8192 + (k>>3)*128 + (k&7)*16 + (b&7)*2
+            // so a pointwise thread (= one k, eight b) writes its gate gradient with ONE 16-byte store
+            constexpr uint32_t idesc = umma_idesc_bf16_bmn(kH, kNB);
             const uint32_t b_base = smem_u32(sB);
             const int j = static_cast<int>(warp) - 8;
             uint64_t db[8];
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
                 const int ks = 4 * q + j;
-                db[q] = umma_desc_k128(b_base + (ks >> 2) * (kNB * 128)) + 2 * (ks & 3);
+                db[q] = umma_desc_mn_interleaved(b_base + ks * 256, 128, 8192);
             }
             for (int s = 0; s < a.T - 1; ++s) {     // no dh needed below t = 0
                 mbar_wait(&dg_ready, s & 1);
@@ -449,10 +452,8 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                 for (int b = 0; b < kHB; ++b) c_old[b] = 0.0f;
             }
         }
-        // loop-invariant shared-memory offsets of this thread's 8 batch rows (gate 0; +4096 per gate)
-        uint32_t row_off[kHB];
-#pragma unroll
-        for (int b = 0; b < kHB; ++b) row_off[b] = swz_off(kNB, bb + b, u);
+        // this thread's 16-byte slot in the MN-major dG operand (gate 0; +2048 per gate)
+        const uint32_t dg_off = static_cast<uint32_t>(half * 8192 + (u >> 3) * 128 + (u & 7) * 16);
         for (int t = a.T - 1, s = 0; t >= 0; --t, ++s) {
             // prefetch the saved activations of step t-1 now: they have the whole step to arrive
             uint4 gq_n[4];
@@ -502,14 +503,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
             if (t > 0) {
                 // B operand of dh_{t-1}^T = Wh * dG_t^T : element (row b, col g*H+u)
 #pragma unroll
-                for (int g = 0; g < 4; ++g) {
-                    const uint32_t v[4] = {pk[g].x, pk[g].y, pk[g].z, pk[g].w};
-#pragma unroll
-                    for (int p = 0; p < 4; ++p) {
-                        sts_bf16(sB, row_off[2 * p] + g * (2 * kNB * 128), v[p] & 0xffffu);
-                        sts_bf16(sB, row_off[2 * p + 1] + g * (2 * kNB * 128), v[p] >> 16);
-                    }
-                }
+                for (int g = 0; g < 4; ++g) *reinterpret_cast<uint4*>(sB + dg_off + g * (kH / 8) * 128) = pk[g];
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
                 __syncwarp();

@@ -229,9 +229,26 @@ __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr, uint32_t 
     return d;
 }
 
+// Shared-memory matrix descriptor for an MN-major (N contiguous) B operand without swizzle:
+// 8x8 core matrices (8 K-rows of 16 bytes = 8 N-elements each, 128 contiguous bytes); LBO =
+// byte stride between core matrices adjacent in K, SBO = byte stride between core matrices
+// adjacent in N.
+__device__ __forceinline__ uint64_t umma_desc_mn_interleaved(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= static_cast<uint64_t>((smem_addr & 0x3FFFF) >> 4);
+    d |= static_cast<uint64_t>(lbo_bytes >> 4) << 16;
+    d |= static_cast<uint64_t>(sbo_bytes >> 4) << 32;
+    d |= 1ull << 46;
+    return d;
+}
+
 // Instruction descriptor: kind::f16, A=B=bf16, D=fp32, both K-major, M x N tile.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t m, uint32_t n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((n >> 3) << 17) | ((m >> 4) << 24);
+}
+// Same, with the B operand MN-major (bit 16).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_bmn(uint32_t m, uint32_t n) {
+    return umma_idesc_bf16(m, n) | (1u << 16);
 }
 
 // ------------------------------------------------------------------ memory model helpers
