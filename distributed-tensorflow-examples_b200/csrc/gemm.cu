@@ -182,6 +182,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc<kTmemCols>(&tmem_base_slot);
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor
+    // prefetch) overlapped with the tail of the previous kernel in the stream; from here on we
+    // touch memory it produced, so wait for it.  Let our own dependent start its prologue now.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -328,7 +333,17 @@ static int launch_gemm(const CUtensorMap* ta, const CUtensorMap* tb, int M, int 
         attr_set = true;
     }
     dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM);
-    gemm_bf16_kernel<BN, kPullB><<<grid, kGemmThreads, smem, st>>>(*ta, *tb, M, N, K, stages, e, b_pull, ldb_pull);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (grid.x * grid.y <= 148) ? 1 : 0;     // only small grids: a waiting dependent must not crowd out work
+    PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, kPullB>, *ta, *tb, M, N, K, stages, e, b_pull, ldb_pull));
     return after_launch(kPullB ? "gemm_bf16_pull" : "gemm_bf16");
 }
 
