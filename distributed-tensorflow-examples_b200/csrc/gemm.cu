@@ -36,6 +36,8 @@ struct EpiArgs {
     float* out_f32;
     int ld_f32;
     float* colsum;
+    int atomic_f32;      // split-K: partial sums are atomically added into out_f32 (caller zeroes it)
+    long long split_stride;   // split-K: CTA z stores its partial at out_f32 + z*split_stride instead (deterministic)
 };
 
 __host__ __device__ constexpr int stage_bytes(int bn) { return kBM * 128 + bn * 128; }
@@ -124,8 +126,13 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, float (&v)[32],
         }
     }
     // ---- fp32 row-major
-    if (e.out_f32 != nullptr && row_ok) {
+    if (e.out_f32 != nullptr && row_ok && e.atomic_f32) {
         float* o = e.out_f32 + static_cast<size_t>(row) * e.ld_f32 + n_base;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+            if (n_base + j < N) atomicAdd(o + j, v[j]);
+    } else if (e.out_f32 != nullptr && row_ok) {
+        float* o = e.out_f32 + static_cast<size_t>(blockIdx.z) * e.split_stride + static_cast<size_t>(row) * e.ld_f32 + n_base;
         if ((N & 3) == 0 && (e.ld_f32 & 3) == 0) {
 #pragma unroll
             for (int g = 0; g < 8; ++g)
@@ -169,7 +176,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     const uint32_t lane = lane_id();
     const int m0 = blockIdx.y * kBM;
     const int n0 = blockIdx.x * BN;
-    const int num_kb = (K + kBK - 1) / kBK;
+    const int total_kb = (K + kBK - 1) / kBK;
+    const int kb_per = (total_kb + static_cast<int>(gridDim.z) - 1) / static_cast<int>(gridDim.z);
+    const int kb0 = static_cast<int>(blockIdx.z) * kb_per;                 // split-K: this CTA's k-block range
+    const int kb1 = (kb0 + kb_per < total_kb) ? kb0 + kb_per : total_kb;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tma_a);
@@ -198,7 +208,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             if (lane == 0) {
                 int s = 0;
                 uint32_t ph = 0;
-                for (int kb = 0; kb < num_kb; ++kb) {
+                for (int kb = kb0; kb < kb1; ++kb) {
                     mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* a_dst = smem + s * kStage;
                     uint8_t* b_dst = a_dst + kBM * 128;
@@ -211,7 +221,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         } else {
             int s = 0;
             uint32_t ph = 0;
-            for (int kb = 0; kb < num_kb; ++kb) {
+            for (int kb = kb0; kb < kb1; ++kb) {
                 if (lane == 0) mbar_wait(&empty_bar[s], ph ^ 1);
                 __syncwarp();
                 uint8_t* a_dst = smem + s * kStage;
@@ -253,7 +263,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             constexpr uint32_t idesc = umma_idesc_bf16(kBM, BN);
             int s = 0;
             uint32_t ph = 0;
-            for (int kb = 0; kb < num_kb; ++kb) {
+            for (int kb = kb0; kb < kb1; ++kb) {
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
                 const uint32_t a_addr = smem_u32(smem + s * kStage);
@@ -263,7 +273,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
                 for (int k = 0; k < kBK / kUmmaK; ++k) {
                     // +32 bytes per K=16 step inside the swizzle atom (>>4 => +2)
-                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+                    umma_bf16(tmem_base, da + 2 * k, db + 2 * k, idesc, (kb > kb0 || k != 0) ? 1u : 0u);
                 }
                 umma_commit(&empty_bar[s]);   // frees the smem slot when these MMAs retire
                 if (++s == stages) { s = 0; ph ^= 1; }
@@ -322,8 +332,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 
 template <int BN, bool kPullB>
 static int launch_gemm(const CUtensorMap* ta, const CUtensorMap* tb, int M, int N, int K,
-                       const EpiArgs& e, cudaStream_t st, const __nv_bfloat16* b_pull, int ldb_pull) {
-    const int num_kb = (K + kBK - 1) / kBK;
+                       const EpiArgs& e, cudaStream_t st, const __nv_bfloat16* b_pull, int ldb_pull, int split_k = 1) {
+    const int num_kb = ((K + kBK - 1) / kBK + split_k - 1) / split_k;
     const int stages = pick_stages(BN, num_kb);
     const size_t smem = static_cast<size_t>(stages) * stage_bytes(BN) + 1024;
     static bool attr_set = false;  // per instantiation
@@ -332,7 +342,7 @@ static int launch_gemm(const CUtensorMap* ta, const CUtensorMap* tb, int M, int 
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
         attr_set = true;
     }
-    dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM);
+    dim3 grid((N + BN - 1) / BN, (M + kBM - 1) / kBM, split_k);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kGemmThreads);
@@ -342,7 +352,7 @@ static int launch_gemm(const CUtensorMap* ta, const CUtensorMap* tb, int M, int 
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = (grid.x * grid.y <= 148) ? 1 : 0;     // only small grids: a waiting dependent must not crowd out work
+    cfg.numAttrs = (grid.x * grid.y * grid.z <= 148) ? 1 : 0;     // only small grids: a waiting dependent must not crowd out work
     PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, kPullB>, *ta, *tb, M, N, K, stages, e, b_pull, ldb_pull));
     return after_launch(kPullB ? "gemm_bf16_pull" : "gemm_bf16");
 }
@@ -396,24 +406,39 @@ static int gemm_entry(const void* A, int lda, const void* B, int ldb, int M, int
     e.out_f32 = epi->out_f32;
     e.ld_f32 = epi->ld_f32;
     e.colsum = epi->colsum;
+    e.atomic_f32 = 0;
+    e.split_stride = 0;
+    // split-K for skinny problems with a long reduction (e.g. dh = dG Wh^T of the large-H LSTM:
+    // M=64, N=4096, K=16384): partial sums are atomically added into the fp32 output
+    int split_k = 1;
+    if (epi->split_k > 1) {
+        if (!epi->out_f32 || epi->out || epi->out_t || epi->colsum || epi->bias || epi->yprev || epi->act)
+            return fail(PSB_ERR_ARG, "%s: split_k needs a plain fp32 output (caller zeroes it)", who);
+        split_k = epi->split_k;
+        const int total_kb = (K + kBK - 1) / kBK;
+        if (split_k > total_kb) split_k = total_kb;
+        if (split_k > 32) split_k = 32;
+        e.split_stride = epi->split_stride;
+        e.atomic_f32 = (split_k > 1 && epi->split_stride == 0) ? 1 : 0;
+    }
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const __nv_bfloat16* bp = static_cast<const __nv_bfloat16*>(B);
     if (pull) {
         switch (bn) {
-            case 16: return launch_gemm<16, true>(ta, tb, M, N, K, e, st, bp, ldb);
-            case 32: return launch_gemm<32, true>(ta, tb, M, N, K, e, st, bp, ldb);
-            case 64: return launch_gemm<64, true>(ta, tb, M, N, K, e, st, bp, ldb);
-            case 128: return launch_gemm<128, true>(ta, tb, M, N, K, e, st, bp, ldb);
-            case 256: return launch_gemm<256, true>(ta, tb, M, N, K, e, st, bp, ldb);
+            case 16: return launch_gemm<16, true>(ta, tb, M, N, K, e, st, bp, ldb, split_k);
+            case 32: return launch_gemm<32, true>(ta, tb, M, N, K, e, st, bp, ldb, split_k);
+            case 64: return launch_gemm<64, true>(ta, tb, M, N, K, e, st, bp, ldb, split_k);
+            case 128: return launch_gemm<128, true>(ta, tb, M, N, K, e, st, bp, ldb, split_k);
+            case 256: return launch_gemm<256, true>(ta, tb, M, N, K, e, st, bp, ldb, split_k);
             default: return fail(PSB_ERR_ARG, "%s: block_n must be 0, 16, 32, 64, 128 or 256", who);
         }
     }
     switch (bn) {
-        case 16: return launch_gemm<16, false>(ta, tb, M, N, K, e, st, nullptr, 0);
-        case 32: return launch_gemm<32, false>(ta, tb, M, N, K, e, st, nullptr, 0);
-        case 64: return launch_gemm<64, false>(ta, tb, M, N, K, e, st, nullptr, 0);
-        case 128: return launch_gemm<128, false>(ta, tb, M, N, K, e, st, nullptr, 0);
-        case 256: return launch_gemm<256, false>(ta, tb, M, N, K, e, st, nullptr, 0);
+        case 16: return launch_gemm<16, false>(ta, tb, M, N, K, e, st, nullptr, 0, split_k);
+        case 32: return launch_gemm<32, false>(ta, tb, M, N, K, e, st, nullptr, 0, split_k);
+        case 64: return launch_gemm<64, false>(ta, tb, M, N, K, e, st, nullptr, 0, split_k);
+        case 128: return launch_gemm<128, false>(ta, tb, M, N, K, e, st, nullptr, 0, split_k);
+        case 256: return launch_gemm<256, false>(ta, tb, M, N, K, e, st, nullptr, 0, split_k);
         default: return fail(PSB_ERR_ARG, "%s: block_n must be 0, 16, 32, 64, 128 or 256", who);
     }
 }

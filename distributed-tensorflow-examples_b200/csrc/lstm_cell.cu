@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(256) lstm_cell_fwd_kernel(const float* __restr
 
 // dh = dh_rec (fp32, from dG_{t+1} Wh^T; nullable at t = T-1) + dy (fp32 from the layer above /
 // the head; nullable).  Writes dG_t bf16 [B, 4H], updates dc in place, atomically adds dbias.
-__global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restrict__ dh_rec, int ld_dh,
+__global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restrict__ dh_rec, int ld_dh, int n_parts, long long part_stride,
                                                             const float* __restrict__ dy, int ld_dy,
                                                             const __nv_bfloat16* __restrict__ gates, const float* __restrict__ c_new,
                                                             const float* __restrict__ c_prev, float* dc,
@@ -53,7 +53,8 @@ __global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restr
     for (int b = blockIdx.y; b < B; b += gridDim.y) {
         const size_t r4 = static_cast<size_t>(b) * 4 * H, ci = static_cast<size_t>(b) * H + u;
         float dh = 0.0f;
-        if (dh_rec != nullptr) dh += dh_rec[static_cast<size_t>(b) * ld_dh + u];
+        if (dh_rec != nullptr)
+            for (int p = 0; p < n_parts; ++p) dh += dh_rec[p * part_stride + static_cast<size_t>(b) * ld_dh + u];
         if (dy != nullptr) dh += dy[static_cast<size_t>(b) * ld_dy + u];
         const float ig = __bfloat162float(gates[r4 + u]), jg = __bfloat162float(gates[r4 + H + u]);
         const float fg = __bfloat162float(gates[r4 + 2 * H + u]), og = __bfloat162float(gates[r4 + 3 * H + u]);
@@ -108,14 +109,14 @@ extern "C" int psb_lstm_cell_fwd(const float* gx, int ld_gx, const float* gh, in
     return after_launch("lstm_cell_fwd");
 }
 
-extern "C" int psb_lstm_cell_bwd(const float* dh_rec, int ld_dh, const float* dy, int ld_dy, const void* gates,
+extern "C" int psb_lstm_cell_bwd(const float* dh_rec, int ld_dh, int n_parts, long long part_stride, const float* dy, int ld_dy, const void* gates,
                                  const float* c_new, const float* c_prev, float* dc, void* dg, int ld_dg,
                                  float* dbias, int B, int H, void* stream) {
     using namespace psb;
     if (!gates || !c_new || !dc || !dg || B < 1 || H < 1) return fail(PSB_ERR_ARG, "psb_lstm_cell_bwd: bad argument");
     dim3 grid((H + 255) / 256, B < 16 ? B : 16);
     lstm_cell_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        dh_rec, ld_dh, dy, ld_dy, static_cast<const __nv_bfloat16*>(gates), c_new, c_prev, dc,
+        dh_rec, ld_dh, n_parts < 1 ? 1 : n_parts, part_stride, dy, ld_dy, static_cast<const __nv_bfloat16*>(gates), c_new, c_prev, dc,
         static_cast<__nv_bfloat16*>(dg), ld_dg, dbias, B, H);
     return after_launch("lstm_cell_bwd");
 }

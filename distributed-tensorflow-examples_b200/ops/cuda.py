@@ -85,7 +85,7 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
          act: int = ACT_NONE, yprev: Optional[BMat] = None, dact: int = 0,
          out: Optional[BMat] = None, out_t: Optional[BMat] = None,
          out_f32: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
-         block_n: int = 0, k: Optional[int] = None) -> None:
+         block_n: int = 0, k: Optional[int] = None, split_k: int = 1, split_stride: int = 0) -> None:
     """``acc = alpha * a @ b.T`` (a: [M,K], b: [N,K]) with the fused epilogue of
     ``psb_gemm_bf16``.  ``k`` overrides the reduction length (defaults to ``a.cols``)."""
     M, N = a.rows, b.rows
@@ -107,6 +107,8 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
     e.ld_f32 = out_f32.stride(0) if out_f32 is not None and out_f32.dim() == 2 else (
         N if out_f32 is not None else 0)
     e.colsum = _ptr(colsum)
+    e.split_k = int(split_k)
+    e.split_stride = int(split_stride)
     if out is not None and (out.rows != M or out.cols != N):
         raise ValueError("gemm: out must be [%d,%d]" % (M, N))
     if out_t is not None and (out_t.rows != N or out_t.cols != M):
@@ -261,7 +263,7 @@ def uniform_noise(rows: int, cols: int, lo: float, hi: float, seed: int,
 # --------------------------------------------------------------------------- large-H LSTM path
 _lib.register_signature("psb_lstm_cell_fwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_float, c_void_p,
                                               c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p])
-_lib.register_signature("psb_lstm_cell_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
+_lib.register_signature("psb_lstm_cell_bwd", [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                               c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_void_p])
 _lib.register_signature("psb_transpose_bf16", [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p])
 
@@ -279,8 +281,12 @@ def lstm_cell_fwd(gx: torch.Tensor, gh: torch.Tensor, bias: torch.Tensor, forget
 def lstm_cell_bwd(dh_rec: Optional[torch.Tensor], dy: Optional[torch.Tensor], gates: torch.Tensor,
                   c_new: torch.Tensor, c_prev: Optional[torch.Tensor], dc: torch.Tensor, dg: BMat,
                   dbias: Optional[torch.Tensor]) -> None:
+    """``dh_rec`` may be ``[B,H]`` or ``[parts,B,H]`` (split-K partial sums, added here)."""
     B, H = dc.shape
-    check(_lib.lib().psb_lstm_cell_bwd(_ptr(dh_rec), dh_rec.stride(0) if dh_rec is not None else 0,
+    parts, pstride = 1, 0
+    if dh_rec is not None and dh_rec.dim() == 3:
+        parts, pstride = dh_rec.shape[0], dh_rec.stride(0)
+    check(_lib.lib().psb_lstm_cell_bwd(_ptr(dh_rec), dh_rec.stride(-2) if dh_rec is not None else 0, parts, pstride,
                                        _ptr(dy), dy.stride(0) if dy is not None else 0, gates.data_ptr(),
                                        c_new.data_ptr(), _ptr(c_prev), dc.data_ptr(), dg.ptr, dg.ld,
                                        _ptr(dbias), B, H, current_stream_ptr()), "psb_lstm_cell_bwd")

@@ -61,6 +61,10 @@ typedef struct psb_epilogue {
     float* out_f32;
     int ld_f32;
     float* colsum;
+    int split_k;       /* > 1: split the reduction over this many CTAs; requires out_f32 only */
+    long long split_stride; /* elements between the split_k partial outputs (split z writes out_f32 +
+                          z*split_stride, the consumer adds them: deterministic); 0 = atomically add all
+                          partials into out_f32, which the caller has zeroed */
 } psb_epilogue_t;
 
 int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
@@ -113,13 +117,14 @@ int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const
  * one SM (the scaled 2-layer H=4096 configuration): the gate GEMMs run through psb_gemm_bf16.
  * Forward: pre = gx + gh + bias (fp32 [B,4H], gate order i,j,f,o), c fp32 [B,H] updated in place,
  * h_out bf16 [B, ld_h]; optional saves for backward (activated gates bf16 [B,4H], c fp32 [B,H]).
- * Backward: dh = dh_rec + dy (either may be NULL), dc fp32 [B,H] updated in place, dg bf16
+ * Backward: dh = sum of the n_parts partial dh_rec buffers (part_stride elements apart: the
+ * split-K outputs of the dh GEMM) + dy (either may be NULL), dc fp32 [B,H] updated in place, dg bf16
  * [B, ld_dg] = gate gradients, dbias fp32 [4H] += column sums (atomic).
  * ref: rnn.BasicLSTMCell / static_rnn, lstm:50-52, scaled per BASELINE.json config #4. */
 int psb_lstm_cell_fwd(const float* gx, int ld_gx, const float* gh, int ld_gh, const float* bias,
                       float forget_bias, float* c, void* h_out, int ld_h, void* gates_save,
                       float* c_save, int B, int H, void* stream);
-int psb_lstm_cell_bwd(const float* dh_rec, int ld_dh, const float* dy, int ld_dy, const void* gates,
+int psb_lstm_cell_bwd(const float* dh_rec, int ld_dh, int n_parts, long long part_stride, const float* dy, int ld_dy, const void* gates,
                       const float* c_new, const float* c_prev, float* dc, void* dg, int ld_dg,
                       float* dbias, int B, int H, void* stream);
 /* out[c][r] = in[r][c], bf16, leading dimensions in elements. */

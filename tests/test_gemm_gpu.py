@@ -95,3 +95,23 @@ def test_gemm_pull_variant_matches(M, N, K, bn):
     ref = torch.sigmoid(A.float() @ B.float().t() + bias)
     assert (o2.float() - ref).abs().max().item() < 2e-2
     assert torch.equal(o1.t, o2.t)
+
+
+@pytest.mark.parametrize("split,stride", [(2, 0), (4, 0), (2, 1), (4, 1)])
+def test_gemm_split_k(split, stride):
+    """Split-K: atomics into a zeroed fp32 output (stride 0) or separate partial buffers."""
+    from psb200.ops import cuda as K_
+    M, N, K = 64, 256, 2048
+    a, b = _mats(M, N, K, 7)
+    A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
+    ref = A.float() @ B.float().t()
+    if stride == 0:
+        out = torch.zeros(M, N, device="cuda")
+        K_.gemm(A, B, out_f32=out, split_k=split)
+        got = out
+    else:
+        parts = torch.full((split, M, N), float("nan"), device="cuda")
+        K_.gemm(A, B, out_f32=parts[0], split_k=split, split_stride=parts.stride(0))
+        got = parts.sum(0)
+    torch.cuda.synchronize()
+    assert torch.allclose(got, ref, atol=2e-3 * ref.abs().max().item(), rtol=1e-4)
