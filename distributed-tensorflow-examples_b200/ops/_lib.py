@@ -70,9 +70,15 @@ def lib():
     global _lib
     if _lib is None:
         if not os.path.exists(LIB_PATH):
-            raise KernelLibraryError(
-                "kernel library %s not found — run `python -m psb200.build` "
-                "(or __graft_entry__.build())" % LIB_PATH)
+            # not built yet (fresh checkout): build in-tree now — nvcc is part of the image; if that
+            # fails there is no fallback path, the error below is final
+            try:
+                from ..build import build_kernels
+                build_kernels()
+            except Exception as e:
+                raise KernelLibraryError(
+                    "kernel library %s not found and building it failed (%s) — run "
+                    "`python -m psb200.build`" % (LIB_PATH, e))
         handle = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
         _declare(handle)
         _lib = handle
