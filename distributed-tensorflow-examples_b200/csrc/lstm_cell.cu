@@ -18,6 +18,10 @@ __global__ void __launch_bounds__(256) lstm_cell_fwd_kernel(const float* __restr
                                                             const float* __restrict__ bias, float forget_bias,
                                                             float* c, __nv_bfloat16* h_out, int ld_h,
                                                             __nv_bfloat16* gates_save, float* c_save, int B, int H) {
+    // programmatic dependent launch: our launch overlapped the producing GEMM's tail; the next
+    // GEMM may start its prologue (barrier init, TMEM allocation) while we run
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int u = blockIdx.x * blockDim.x + threadIdx.x;
     const int b = blockIdx.y;
     if (u >= H || b >= B) return;
@@ -47,31 +51,53 @@ __global__ void __launch_bounds__(256) lstm_cell_bwd_kernel(const float* __restr
                                                             const __nv_bfloat16* __restrict__ gates, const float* __restrict__ c_new,
                                                             const float* __restrict__ c_prev, float* dc,
                                                             __nv_bfloat16* dg, int ld_dg, float* dbias, int B, int H) {
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     const int u = blockIdx.x * blockDim.x + threadIdx.x;
     if (u >= H) return;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int b = blockIdx.y; b < B; b += gridDim.y) {
-        const size_t r4 = static_cast<size_t>(b) * 4 * H, ci = static_cast<size_t>(b) * H + u;
-        float dh = 0.0f;
-        if (dh_rec != nullptr)
-            for (int p = 0; p < n_parts; ++p) dh += dh_rec[p * part_stride + static_cast<size_t>(b) * ld_dh + u];
-        if (dy != nullptr) dh += dy[static_cast<size_t>(b) * ld_dy + u];
-        const float ig = __bfloat162float(gates[r4 + u]), jg = __bfloat162float(gates[r4 + H + u]);
-        const float fg = __bfloat162float(gates[r4 + 2 * H + u]), og = __bfloat162float(gates[r4 + 3 * H + u]);
-        const float tc = fast_tanh(c_new[ci]);
-        const float co = c_prev != nullptr ? c_prev[ci] : 0.0f;
-        const float dcv = fmaf(dh * og, 1.0f - tc * tc, dc[ci]);
-        const float d_o = dh * tc * og * (1.0f - og);
-        const float d_i = dcv * jg * ig * (1.0f - ig);
-        const float d_j = dcv * ig * (1.0f - jg * jg);
-        const float d_f = dcv * co * fg * (1.0f - fg);
-        dc[ci] = dcv * fg;
-        __nv_bfloat16* o = dg + static_cast<size_t>(b) * ld_dg;
-        o[u] = __float2bfloat16_rn(d_i);
-        o[H + u] = __float2bfloat16_rn(d_j);
-        o[2 * H + u] = __float2bfloat16_rn(d_f);
-        o[3 * H + u] = __float2bfloat16_rn(d_o);
-        acc[0] += d_i; acc[1] += d_j; acc[2] += d_f; acc[3] += d_o;
+    // each thread walks batch rows blockIdx.y, +gridDim.y, ...; rows are processed four at a time
+    // with every load issued before the first use (the kernel is pure memory latency)
+    constexpr int R = 4;
+    for (int b0 = blockIdx.y; b0 < B; b0 += gridDim.y * R) {
+        float dh[R], gi[R], gj[R], gf[R], go[R], cn[R], co[R], dcv_in[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int b = b0 + r * gridDim.y;
+            dh[r] = gi[r] = gj[r] = gf[r] = go[r] = cn[r] = co[r] = dcv_in[r] = 0.0f;
+            if (b < B) {
+                const size_t r4 = static_cast<size_t>(b) * 4 * H, ci = static_cast<size_t>(b) * H + u;
+                if (dh_rec != nullptr)
+                    for (int p = 0; p < n_parts; ++p) dh[r] += dh_rec[p * part_stride + static_cast<size_t>(b) * ld_dh + u];
+                if (dy != nullptr) dh[r] += dy[static_cast<size_t>(b) * ld_dy + u];
+                gi[r] = __bfloat162float(gates[r4 + u]);
+                gj[r] = __bfloat162float(gates[r4 + H + u]);
+                gf[r] = __bfloat162float(gates[r4 + 2 * H + u]);
+                go[r] = __bfloat162float(gates[r4 + 3 * H + u]);
+                cn[r] = c_new[ci];
+                co[r] = c_prev != nullptr ? c_prev[ci] : 0.0f;
+                dcv_in[r] = dc[ci];
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int b = b0 + r * gridDim.y;
+            if (b >= B) continue;
+            const size_t ci = static_cast<size_t>(b) * H + u;
+            const float tc = fast_tanh(cn[r]);
+            const float dcv = fmaf(dh[r] * go[r], 1.0f - tc * tc, dcv_in[r]);
+            const float d_o = dh[r] * tc * go[r] * (1.0f - go[r]);
+            const float d_i = dcv * gj[r] * gi[r] * (1.0f - gi[r]);
+            const float d_j = dcv * gi[r] * (1.0f - gj[r] * gj[r]);
+            const float d_f = dcv * co[r] * gf[r] * (1.0f - gf[r]);
+            dc[ci] = dcv * gf[r];
+            __nv_bfloat16* o = dg + static_cast<size_t>(b) * ld_dg;
+            o[u] = __float2bfloat16_rn(d_i);
+            o[H + u] = __float2bfloat16_rn(d_j);
+            o[2 * H + u] = __float2bfloat16_rn(d_f);
+            o[3 * H + u] = __float2bfloat16_rn(d_o);
+            acc[0] += d_i; acc[1] += d_j; acc[2] += d_f; acc[3] += d_o;
+        }
     }
     if (dbias != nullptr) {
 #pragma unroll
@@ -102,10 +128,18 @@ extern "C" int psb_lstm_cell_fwd(const float* gx, int ld_gx, const float* gh, in
     using namespace psb;
     if (!gx || !gh || !bias || !c || !h_out || B < 1 || H < 1) return fail(PSB_ERR_ARG, "psb_lstm_cell_fwd: bad argument");
     if ((gates_save != nullptr) != (c_save != nullptr)) return fail(PSB_ERR_ARG, "psb_lstm_cell_fwd: gates_save and c_save go together");
-    dim3 grid((H + 255) / 256, B);
-    lstm_cell_fwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        gx, ld_gx, gh, ld_gh, bias, forget_bias, c, static_cast<__nv_bfloat16*>(h_out), ld_h,
-        static_cast<__nv_bfloat16*>(gates_save), c_save, B, H);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((H + 255) / 256, B);
+    cfg.blockDim = dim3(256);
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_cell_fwd_kernel, gx, ld_gx, gh, ld_gh, bias, forget_bias, c,
+                                   static_cast<__nv_bfloat16*>(h_out), ld_h, static_cast<__nv_bfloat16*>(gates_save),
+                                   c_save, B, H));
     return after_launch("lstm_cell_fwd");
 }
 
@@ -114,10 +148,18 @@ extern "C" int psb_lstm_cell_bwd(const float* dh_rec, int ld_dh, int n_parts, lo
                                  float* dbias, int B, int H, void* stream) {
     using namespace psb;
     if (!gates || !c_new || !dc || !dg || B < 1 || H < 1) return fail(PSB_ERR_ARG, "psb_lstm_cell_bwd: bad argument");
-    dim3 grid((H + 255) / 256, B < 16 ? B : 16);
-    lstm_cell_bwd_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        dh_rec, ld_dh, n_parts < 1 ? 1 : n_parts, part_stride, dy, ld_dy, static_cast<const __nv_bfloat16*>(gates), c_new, c_prev, dc,
-        static_cast<__nv_bfloat16*>(dg), ld_dg, dbias, B, H);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((H + 255) / 256, B < 16 ? B : 16);
+    cfg.blockDim = dim3(256);
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_cell_bwd_kernel, dh_rec, ld_dh, n_parts < 1 ? 1 : n_parts, part_stride, dy,
+                                   ld_dy, static_cast<const __nv_bfloat16*>(gates), c_new, c_prev, dc,
+                                   static_cast<__nv_bfloat16*>(dg), ld_dg, dbias, B, H));
     return after_launch("lstm_cell_bwd");
 }
 

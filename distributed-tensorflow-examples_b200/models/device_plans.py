@@ -275,11 +275,14 @@ class ScaledLstmPlan(DevicePlan):
         self.c = torch.zeros(B, H, device=dev)
         self.h0 = BMat(B, H, dev)                                    # zero initial state
         self.dG, self.dGT = BMat(TB, 4 * H, dev), BMat(4 * H, TB, dev)
-        # dh = dG Wh^T is skinny (M = B) with a 4H-long reduction.  Split-K into partial buffers is
-        # supported (and ~1.5x faster in isolation with a cold L2), but inside the timestep loop the
-        # unsplit kernel re-reads Wh in the same order every step and wins on L2 hits: measured
-        # 146.6 ms/step (split 1) vs 164.8 ms/step (split 2) at H=4096, T=512, B=64.
-        self.split_k = 1
+        # The recurrent GEMMs are skinny (M = B).  Measured in situ at H=4096, T=512, B=64 (ms/step):
+        # auto tiles 156.1 | fwd BN=128 151.1 | + bwd split-K 2, BN=64 127.5 | bwd BN=128 133.0.
+        # One wave of <= 148 CTAs keeps programmatic dependent launch on (see gemm.cu); dh = dG Wh^T
+        # has a 4H-long reduction, so it is split in two partial buffers that the cell kernel adds.
+        big = H >= 2048
+        self.split_k = 2 if big else 1
+        self.bn_fwd = 128 if big else 0
+        self.bn_bwd = 64 if big else 0
         self.dh_rec = torch.zeros(self.split_k, B, H, device=dev)
         self.dc = torch.zeros(B, H, device=dev)
         self.dY = torch.zeros(TB, H, device=dev) if L > 1 else None  # gradient arriving from the layer above
@@ -307,7 +310,7 @@ class ScaledLstmPlan(DevicePlan):
             self.c.zero_()
             for t in range(T):
                 hprev = self.h0 if t == 0 else self._rows(self.Hall[l], t - 1)
-                K.gemm(hprev, wh_t, out_f32=self.gh)
+                K.gemm(hprev, wh_t, out_f32=self.gh, block_n=self.bn_fwd)
                 K.lstm_cell_fwd(self.gx[t * B:(t + 1) * B], self.gh, bias, 1.0, self.c, self._rows(self.Hall[l], t),
                                 self.gates[l][t * B:(t + 1) * B] if train else None,
                                 self.c_all[l][t * B:(t + 1) * B] if train else None)
@@ -346,7 +349,7 @@ class ScaledLstmPlan(DevicePlan):
                                 self._rows(self.dG, t), s.grad(n("bias%d" % l)))
                 if t > 0:
                     K.gemm(self._rows(self.dG, t), wh, out_f32=self.dh_rec[0], split_k=self.split_k,
-                           split_stride=self.dh_rec.stride(0))
+                           split_stride=self.dh_rec.stride(0), block_n=self.bn_bwd)
             # weight gradients of this layer in two large GEMMs over all (t, b)
             K.transpose_bf16(self.dG, self.dGT)
             # [h_{t-1}]^T: column block t holds h_{t-1}; block 0 is the zero state
