@@ -38,6 +38,7 @@ struct EpiArgs {
     float* colsum;
     int atomic_f32;      // split-K: partial sums are atomically added into out_f32 (caller zeroes it)
     long long split_stride;   // split-K: CTA z stores its partial at out_f32 + z*split_stride instead (deterministic)
+    int b_static;             // B was NOT written by the preceding kernel: its first stages may be fetched before griddepcontrol.wait
 };
 
 __host__ __device__ constexpr int stage_bytes(int bn) { return kBM * 128 + bn * 128; }
@@ -191,6 +192,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         mbar_init(&tmem_full_bar, 1);
         fence_mbar_init();
     }
+    // B operand that does not depend on the previous kernel (weights): start streaming its first
+    // stages now, under the previous kernel's tail; A (activations) follows after the wait.
+    int pre = 0;
+    if (!kPullB && epi.b_static) {
+        pre = (kb1 - kb0 < stages) ? (kb1 - kb0) : stages;
+        if (warp == 0 && lane == 0) {
+            for (int s = 0; s < pre; ++s) {
+                mbar_expect_tx(&full_bar[s], kStage);
+                tma_load_2d(smem + s * kStage + kBM * 128, &tma_b, &full_bar[s], (kb0 + s) * kBK, n0);
+            }
+        }
+    }
     if (warp == 1) tmem_alloc<kTmemCols>(&tmem_base_slot);
     // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor
     // prefetch) overlapped with the tail of the previous kernel in the stream; from here on we
@@ -209,12 +222,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                 int s = 0;
                 uint32_t ph = 0;
                 for (int kb = kb0; kb < kb1; ++kb) {
-                    mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* a_dst = smem + s * kStage;
                     uint8_t* b_dst = a_dst + kBM * 128;
-                    mbar_expect_tx(&full_bar[s], kStage);
-                    tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
-                    tma_load_2d(b_dst, &tma_b, &full_bar[s], kb * kBK, n0);
+                    if (kb - kb0 < pre) {
+                        // B of this stage is already in flight (and its expect_tx armed)
+                        tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
+                    } else {
+                        mbar_wait(&empty_bar[s], ph ^ 1);
+                        mbar_expect_tx(&full_bar[s], kStage);
+                        tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
+                        tma_load_2d(b_dst, &tma_b, &full_bar[s], kb * kBK, n0);
+                    }
                     if (++s == stages) { s = 0; ph ^= 1; }
                 }
             }
@@ -408,6 +426,7 @@ static int gemm_entry(const void* A, int lda, const void* B, int ldb, int M, int
     e.colsum = epi->colsum;
     e.atomic_f32 = 0;
     e.split_stride = 0;
+    e.b_static = epi->b_static;
     // split-K for skinny problems with a long reduction (e.g. dh = dG Wh^T of the large-H LSTM:
     // M=64, N=4096, K=16384): partial sums are atomically added into the fp32 output
     int split_k = 1;

@@ -86,9 +86,9 @@ class EncoderPlan(DevicePlan):
         K.cast_transpose(self.inputs["x"], self.act[0], self.act_t[0] if need_t else None)
         for l in range(3):
             K.gemm(self.act[l], s.wt_src(n(self.wkeys[l])), bias=s.vec_src(n(self.bkeys[l])), act=ACT_SIGMOID,
-                   out=self.act[l + 1], out_t=self.act_t[l + 1] if need_t else None)
+                   out=self.act[l + 1], out_t=self.act_t[l + 1] if need_t else None, b_static=True)
         K.gemm(self.act[3], s.wt_src(n(self.wkeys[3])), bias=s.vec_src(n(self.bkeys[3])), act=ACT_SIGMOID,
-               out_f32=self.y)
+               out_f32=self.y, b_static=True)
 
     def forward_backward(self) -> None:
         s, n = self.store, self._name
@@ -104,7 +104,7 @@ class EncoderPlan(DevicePlan):
                 K.gemm(self.act_t[l], self.dz_t[l + 1], out_f32=s.grad(n(self.wkeys[l])))
             if l > 0:
                 K.gemm(self.dz[l + 1], s.w_src(n(self.wkeys[l])), yprev=self.act[l], dact=1,
-                       out=self.dz[l], out_t=self.dz_t[l], colsum=s.grad(n(self.bkeys[l - 1])))
+                       out=self.dz[l], out_t=self.dz_t[l], colsum=s.grad(n(self.bkeys[l - 1])), b_static=True)
         self._join()
 
     def kernels_per_step(self) -> int:
@@ -150,13 +150,13 @@ class GanPlan(DevicePlan):
         else:
             K.cast_transpose(self.inputs["z"], self.Z, self.ZT)
         K.gemm(self.Z, s.wt_src(n("w_gen_hidden1")), bias=s.vec_src(n("b_gen_hidden1")), act=ACT_RELU,
-               out=self.GH, out_t=self.GHT)
+               out=self.GH, out_t=self.GHT, b_static=True)
         K.gemm(self.GH, s.wt_src(n("w_gen_out")), bias=s.vec_src(n("b_gen_out")), act=ACT_SIGMOID,
-               out=self.Din_fake, out_t=self.DinT_fake)
+               out=self.Din_fake, out_t=self.DinT_fake, b_static=True)
         K.gemm(self.Din, s.wt_src(n("w_disc_hidden1")), bias=s.vec_src(n("b_disc_hidden1")), act=ACT_RELU,
-               out=self.DH, out_t=self.DHT)
+               out=self.DH, out_t=self.DHT, b_static=True)
         K.gemm(self.DH, s.wt_src(n("w_disc_out")), bias=s.vec_src(n("b_disc_out")), act=ACT_NONE,
-               out_f32=self.logit)
+               out_f32=self.logit, b_static=True)
 
     def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
         s, n, B = self.store, self._name, self.B
@@ -170,15 +170,15 @@ class GanPlan(DevicePlan):
             with torch.cuda.stream(self.side):
                 K.gemm(self.DHT, self.d_disc_t, out_f32=s.grad(n("w_disc_out")))
                 K.gemm(self.d_disc, s.w_src(n("w_disc_out")), yprev=self.DH, dact=2, out=self.dZ1, out_t=self.dZ1T,
-                       colsum=s.grad(n("b_disc_hidden1")))
+                       colsum=s.grad(n("b_disc_hidden1")), b_static=True)
                 K.gemm(self.DinT, self.dZ1T, out_f32=s.grad(n("w_disc_hidden1")))
         if gen:
-            K.gemm(self.d_gen, s.w_src(n("w_disc_out")), yprev=self.DH_fake, dact=2, out=self.dZ1f)
+            K.gemm(self.d_gen, s.w_src(n("w_disc_out")), yprev=self.DH_fake, dact=2, out=self.dZ1f, b_static=True)
             K.gemm(self.dZ1f, s.w_src(n("w_disc_hidden1")), yprev=self.Din_fake, dact=1, out=self.dZo,
-                   out_t=self.dZoT, colsum=s.grad(n("b_gen_out")))
+                   out_t=self.dZoT, colsum=s.grad(n("b_gen_out")), b_static=True)
             K.gemm(self.GHT, self.dZoT, out_f32=s.grad(n("w_gen_out")))
             K.gemm(self.dZo, s.w_src(n("w_gen_out")), yprev=self.GH, dact=2, out=self.dZh, out_t=self.dZhT,
-                   colsum=s.grad(n("b_gen_hidden1")))
+                   colsum=s.grad(n("b_gen_hidden1")), b_static=True)
             K.gemm(self.ZT, self.dZhT, out_f32=s.grad(n("w_gen_hidden1")))
         if disc:
             self._join()
@@ -223,7 +223,7 @@ class LstmPlan(DevicePlan):
         K.lstm_fwd(self.inputs["x"], s.wt(n("kernel")), s.vec_src(n("bias")), lstm_mod.forget_bias,
                    self.h_last, self.h_last_t if train else None, self.saved if train else None,
                    wt_ptr=wt_ptr)
-        K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits)
+        K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits, b_static=True)
 
     def evaluate(self) -> None:
         """Fills ``losses['loss']`` and ``correct`` for the current inputs without touching
@@ -242,7 +242,7 @@ class LstmPlan(DevicePlan):
         self._fork()
         with torch.cuda.stream(self.side):
             K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
-        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh)
+        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh, b_static=True)
         K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
         K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")))
         self._join()
@@ -306,17 +306,17 @@ class ScaledLstmPlan(DevicePlan):
             wt = s.wt_src(n("kernel%d" % l))                  # [4H, I+H]
             wx_t, wh_t = wt.cols_view(0, I), wt.cols_view(I, I + H)
             bias = s.vec_src(n("bias%d" % l))
-            K.gemm(inp, wx_t, out_f32=self.gx)                # all timesteps at once
+            K.gemm(inp, wx_t, out_f32=self.gx, b_static=True)                # all timesteps at once
             self.c.zero_()
             for t in range(T):
                 hprev = self.h0 if t == 0 else self._rows(self.Hall[l], t - 1)
-                K.gemm(hprev, wh_t, out_f32=self.gh, block_n=self.bn_fwd)
+                K.gemm(hprev, wh_t, out_f32=self.gh, block_n=self.bn_fwd, b_static=True)
                 K.lstm_cell_fwd(self.gx[t * B:(t + 1) * B], self.gh, bias, 1.0, self.c, self._rows(self.Hall[l], t),
                                 self.gates[l][t * B:(t + 1) * B] if train else None,
                                 self.c_all[l][t * B:(t + 1) * B] if train else None)
             inp = self.Hall[l]
         h_last = self._rows(self.Hall[-1], T - 1)
-        K.gemm(h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits)
+        K.gemm(h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits, b_static=True)
 
     def forward_backward(self) -> None:
         s, n, mdl, B = self.store, self._name, self.model, self.B
@@ -329,7 +329,7 @@ class ScaledLstmPlan(DevicePlan):
         h_last = self._rows(self.Hall[-1], T - 1)
         K.transpose_bf16(h_last, self.h_last_t)
         K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
-        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh_top)
+        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh_top, b_static=True)
         for l in range(mdl.L - 1, -1, -1):
             I = mdl.in_dim(l)
             w = s.w_src(n("kernel%d" % l))                    # [I+H, 4H]
@@ -349,7 +349,7 @@ class ScaledLstmPlan(DevicePlan):
                                 self._rows(self.dG, t), s.grad(n("bias%d" % l)))
                 if t > 0:
                     K.gemm(self._rows(self.dG, t), wh, out_f32=self.dh_rec[0], split_k=self.split_k,
-                           split_stride=self.dh_rec.stride(0), block_n=self.bn_bwd)
+                           split_stride=self.dh_rec.stride(0), block_n=self.bn_bwd, b_static=True)
             # weight gradients of this layer in two large GEMMs over all (t, b)
             K.transpose_bf16(self.dG, self.dGT)
             # [h_{t-1}]^T: column block t holds h_{t-1}; block 0 is the zero state
@@ -362,7 +362,7 @@ class ScaledLstmPlan(DevicePlan):
             else:
                 K.transpose_bf16(self.Hall[l - 1], self.XinT)
                 K.gemm(self.XinT, self.dGT, out_f32=gk[:I])
-                K.gemm(self.dG, wx, out_f32=self.dY)          # gradient to the layer below, all timesteps
+                K.gemm(self.dG, wx, out_f32=self.dY, b_static=True)          # gradient to the layer below, all timesteps
 
     def evaluate(self) -> None:
         self.forward(train=False)

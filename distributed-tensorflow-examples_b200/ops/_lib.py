@@ -24,7 +24,7 @@ class Epilogue(Structure):
         ("out", c_void_p), ("ld_out", c_int),
         ("out_t", c_void_p), ("ld_out_t", c_int),
         ("out_f32", c_void_p), ("ld_f32", c_int),
-        ("colsum", c_void_p), ("split_k", c_int), ("split_stride", ctypes.c_longlong),
+        ("colsum", c_void_p), ("split_k", c_int), ("split_stride", ctypes.c_longlong), ("b_static", c_int),
     ]
 
 

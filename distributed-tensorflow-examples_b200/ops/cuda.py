@@ -85,9 +85,12 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
          act: int = ACT_NONE, yprev: Optional[BMat] = None, dact: int = 0,
          out: Optional[BMat] = None, out_t: Optional[BMat] = None,
          out_f32: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
-         block_n: int = 0, k: Optional[int] = None, split_k: int = 1, split_stride: int = 0) -> None:
+         block_n: int = 0, k: Optional[int] = None, split_k: int = 1, split_stride: int = 0,
+         b_static: bool = False) -> None:
     """``acc = alpha * a @ b.T`` (a: [M,K], b: [N,K]) with the fused epilogue of
-    ``psb_gemm_bf16``.  ``k`` overrides the reduction length (defaults to ``a.cols``)."""
+    ``psb_gemm_bf16``.  ``k`` overrides the reduction length (defaults to ``a.cols``).
+    ``b_static=True`` promises that ``b`` (a weight copy) was not written by the kernel launched
+    just before this one, which lets the kernel prefetch it under that kernel's tail."""
     M, N = a.rows, b.rows
     K = int(k) if k is not None else a.cols
     if k is None and a.cols != b.cols:
@@ -109,6 +112,7 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
     e.colsum = _ptr(colsum)
     e.split_k = int(split_k)
     e.split_stride = int(split_stride)
+    e.b_static = 1 if b_static else 0
     if out is not None and (out.rows != M or out.cols != N):
         raise ValueError("gemm: out must be [%d,%d]" % (M, N))
     if out_t is not None and (out_t.rows != N or out_t.cols != M):

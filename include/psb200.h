@@ -65,6 +65,9 @@ typedef struct psb_epilogue {
     long long split_stride; /* elements between the split_k partial outputs (split z writes out_f32 +
                           z*split_stride, the consumer adds them: deterministic); 0 = atomically add all
                           partials into out_f32, which the caller has zeroed */
+    int b_static;      /* 1: B (e.g. a weight copy) was not produced by the kernel launched just before this
+                          one on the stream, so its first pipeline stages may be fetched while that kernel is
+                          still finishing (programmatic dependent launch); 0 when in doubt */
 } psb_epilogue_t;
 
 int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
