@@ -101,6 +101,27 @@ class Supervisor:
             t = threading.Thread(target=self._aggregate_loop, name="SyncReplicasQueueRunner", daemon=True)
             t.start()
             self._threads.append(t)
+        t = threading.Thread(target=self._step_counter_loop, name="SVStepCounterThread", daemon=True)
+        t.start()
+        self._threads.append(t)
+
+    def _step_counter_loop(self, period: float = 5.0) -> None:
+        """The chief's ``global_step/sec`` summary (TF's SVStepCounterThread): one JSON line per
+        period appended to ``<logdir>/events.jsonl``."""
+        from .control.client import PsError
+        path = os.path.join(self.logdir, "events.jsonl")
+        last_t, last_step = time.time(), None
+        while not self._stop.wait(period):
+            try:
+                step = self.store.global_step()
+            except (PsError, ConnectionError, OSError):
+                return
+            now = time.time()
+            if last_step is not None and now > last_t:
+                with open(path, "a") as f:
+                    f.write(json.dumps({"wall_time": now, "global_step": step,
+                                        "global_step/sec": (step - last_step) / (now - last_t)}) + "\n")
+            last_t, last_step = now, step
 
     def save_checkpoint(self) -> Optional[str]:
         with self._save_lock:
