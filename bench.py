@@ -156,7 +156,7 @@ def run_psb200(args):
     if model == "scaled_lstm":
         dims = dict(num_input=args.hidden, timesteps=args.seq, num_hidden=args.hidden, num_layers=args.layers)
     tr = DeviceTrainer(model, rank, world, group, mode=args.mode, seed=args.seed, batch=B,
-                       gan_update=args.gan_update, plan_kwargs=kw, model_kwargs=dims)
+                       gan_update=args.gan_update, plan_kwargs=kw, model_kwargs=dims, bcast=bool(args.bcast))
     tr.initialize()
     batches = synthetic_batches(model, B, 2 if model == "scaled_lstm" else 8, args.seed * 1000 + rank, dims)
     dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
@@ -205,7 +205,7 @@ def run_psb200(args):
             "impl": "psb200",
             "config": {"model": MODEL_LABEL[model] if dims is None else "scaled %d-layer LSTM hidden %d seq %d bf16, SGD" % (args.layers, args.hidden, args.seq),
                        "global_batch": B * world, "seq_len": 28 if model == "lstm" else (args.seq if dims else None),
-                       "parallelism": "dp%d ps-sharded (%s)" % (world, args.mode),
+                       "parallelism": "dp%d ps-sharded (%s%s)" % (world, args.mode, "" if args.bcast else ", pull-fused"),
                        "l2": "flushed between timed iterations (256 MiB write outside the event pairs)",
                        "cuda_graph": tr.graph is not None,
                        "baseline_for_vs": "PyTorch DDP/NCCL rendition, baseline/measured.json" if base else None},
@@ -262,6 +262,7 @@ def main():
     ap.add_argument("--mode", default="sync", choices=["sync", "async"])
     ap.add_argument("--gan_update", default="simultaneous", choices=["simultaneous", "alternating"])
     ap.add_argument("--impl", default="psb200", choices=["psb200", "reference", "torch_ddp"])
+    ap.add_argument("--bcast", type=int, default=1, help="1: push kernel refreshes every rank's arena; 0: consumers pull from the owner")
     ap.add_argument("--seed", type=int, default=0)
     args = ap.parse_args()
     if args.warmup < 3:

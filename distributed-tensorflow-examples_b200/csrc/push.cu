@@ -168,9 +168,18 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                     if (tI < ntiles && r < rows && c < cols) {
                         const size_t i = static_cast<size_t>(r) * cols + c;
                         if (v4) {
-                            for (int rk = 0; rk < a.world; ++rk) {
-                                const float4 t = ld_volatile_v4(a.grad_ptrs[rk] + s.grad_offset + i);
-                                g[u][0] += t.x; g[u][1] += t.y; g[u][2] += t.z; g[u][3] += t.w;
+                            // all ranks' slices first (independent NVLink loads in flight together),
+                            // then the sum in rank order (deterministic)
+                            float4 t[8];
+#pragma unroll
+                            for (int rk = 0; rk < 8; ++rk)
+                                if (rk < a.world) t[rk] = ld_volatile_v4(a.grad_ptrs[rk] + s.grad_offset + i);
+#pragma unroll
+                            for (int rk = 0; rk < 8; ++rk)
+                                if (rk < a.world) { g[u][0] += t[rk].x; g[u][1] += t[rk].y; g[u][2] += t[rk].z; g[u][3] += t[rk].w; }
+                            for (int rk = 8; rk < a.world; ++rk) {
+                                const float4 tt = ld_volatile_v4(a.grad_ptrs[rk] + s.grad_offset + i);
+                                g[u][0] += tt.x; g[u][1] += tt.y; g[u][2] += tt.z; g[u][3] += tt.w;
                             }
                             if (!atomic_sgd) {
                                 const float4 t = *reinterpret_cast<const float4*>(master + i);
@@ -282,9 +291,16 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                     w[j] = v0[j] = v1[j] = g[j];
                     if (i4 < n4) {
                         const size_t i = static_cast<size_t>(i4) * 4;
-                        for (int r = 0; r < a.world; ++r) {
-                            const float4 t = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
-                            g[j].x += t.x; g[j].y += t.y; g[j].z += t.z; g[j].w += t.w;
+                        float4 t[8];
+#pragma unroll
+                        for (int r = 0; r < 8; ++r)
+                            if (r < a.world) t[r] = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
+#pragma unroll
+                        for (int r = 0; r < 8; ++r)
+                            if (r < a.world) { g[j].x += t[r].x; g[j].y += t[r].y; g[j].z += t[r].z; g[j].w += t[r].w; }
+                        for (int r = 8; r < a.world; ++r) {
+                            const float4 tt = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
+                            g[j].x += tt.x; g[j].y += tt.y; g[j].z += tt.z; g[j].w += tt.w;
                         }
                         w[j] = *reinterpret_cast<const float4*>(master + i);
                         if (o.kind > 0) {

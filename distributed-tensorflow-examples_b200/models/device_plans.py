@@ -244,7 +244,9 @@ class LstmPlan(DevicePlan):
             K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
         K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh, b_static=True)
         K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
-        K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")))
+        # reduction over all (t, b) = 3584 columns: two-way split-K; the two partial sums are added
+        # atomically into the zeroed gradient buffer (two addends commute: still deterministic)
+        K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")), split_k=2)
         self._join()
 
     def kernels_per_step(self) -> int:
