@@ -237,6 +237,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
 #pragma unroll
             for (int q = 0; q < 2; ++q)
                 xn[q] = (more && xsrc[q] != nullptr) ? xsrc[q][static_cast<size_t>(t + 1) * a.I] : 0.0f;
+            if (!more) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // head GEMM may set up now
             mbar_wait(&mma_done, t & 1);
             tc_fence_after_sync();
             uint32_t ri[8], rj[8], rf[8], ro[8];
@@ -389,6 +390,9 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         }
         tmem_st_wait();
     }
+    // Wh came from the parameter arena (not written by the kernels just before us): it was loaded
+    // under the tail of the head dgrad GEMM.  From here on we read what those kernels produced.
+    asm volatile("griddepcontrol.wait;" ::: "memory");
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
@@ -455,6 +459,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         // this thread's 16-byte slot in the MN-major dG operand (gate 0; +2048 per gate)
         const uint32_t dg_off = static_cast<uint32_t>(half * 8192 + (u >> 3) * 128 + (u & 7) * 16);
         for (int t = a.T - 1, s = 0; t >= 0; --t, ++s) {
+            if (t == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // wgrad GEMM may set up now
             // prefetch the saved activations of step t-1 now: they have the whole step to arrive
             uint4 gq_n[4];
             float4 cp0 = make_float4(0.f, 0.f, 0.f, 0.f), cp1 = cp0;
@@ -653,6 +658,16 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
         PSB_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr = true;
     }
-    lstm_bwd_kernel<<<(B + kNB - 1) / kNB, kLstmThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((B + kNB - 1) / kNB);
+    cfg.blockDim = dim3(kLstmThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_bwd_kernel, a));
     return after_launch("lstm_bwd");
 }
