@@ -39,6 +39,18 @@ struct EpiArgs {
     int atomic_f32;      // split-K: partial sums are atomically added into out_f32 (caller zeroes it)
     long long split_stride;   // split-K: CTA z stores its partial at out_f32 + z*split_stride instead (deterministic)
     int b_static;             // B was NOT written by the preceding kernel: its first stages may be fetched before griddepcontrol.wait
+    // ---- fused large-H LSTM step (BN == 128 only): B tile = 4 gate blocks x 32 units gathered with four
+    // 32-row TMA boxes, epilogue = the BasicLSTMCell pointwise.  Active when lstm_c != nullptr.
+    const float* lstm_gx;     // fp32 [B, 4H] x-part pre-activations of this timestep
+    int ld_gx;
+    const float* lstm_bias;   // fp32 [4H]
+    float forget_bias;
+    float* lstm_c;            // fp32 [B, H] in/out
+    __nv_bfloat16* lstm_h;    // bf16 [B, ld_lstm_h] out
+    int ld_lstm_h;
+    __nv_bfloat16* lstm_gates;   // bf16 [B, 4H] activated gates (nullable, with lstm_csave)
+    float* lstm_csave;        // fp32 [B, H]
+    int lstm_H;
 };
 
 __host__ __device__ constexpr int stage_bytes(int bn) { return kBM * 128 + bn * 128; }
@@ -157,6 +169,68 @@ __device__ __forceinline__ void epilogue_chunk(const EpiArgs& e, float (&v)[32],
 // reached over NVLink — and written into the same 128B-swizzled smem tile.  That is the
 // parameter pull (all-gather) fused into the consuming GEMM: peer loads of stage s+1.. run
 // under the MMAs of stage s.
+// Pointwise half of a BasicLSTMCell step on one accumulator row: columns [g*32 + j] hold gate g of
+// unit u0 + j.  Eight units at a time: four 8-column TMEM loads, vector loads of gx / bias / c.
+__device__ __forceinline__ void lstm_step_epilogue(const EpiArgs& e, uint32_t t_row, int row, int M, int u0) {
+    const int H = e.lstm_H;
+    const bool ok = row < M;
+    const size_t r_gx = static_cast<size_t>(row) * e.ld_gx, r_c = static_cast<size_t>(row) * H,
+                 r_g = static_cast<size_t>(row) * 4 * H;
+#pragma unroll 1
+    for (int j8 = 0; j8 < 32; j8 += 8) {
+        uint32_t acc[4][8];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) tmem_ld_32x8(t_row + g * 32 + j8, acc[g]);
+        const int u = u0 + j8;
+        float pre[4][8], cv[8];
+        if (ok) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+                const float4 x0 = *reinterpret_cast<const float4*>(e.lstm_gx + r_gx + g * H + u);
+                const float4 x1 = *reinterpret_cast<const float4*>(e.lstm_gx + r_gx + g * H + u + 4);
+                const float4 b0 = __ldg(reinterpret_cast<const float4*>(e.lstm_bias + g * H + u));
+                const float4 b1 = __ldg(reinterpret_cast<const float4*>(e.lstm_bias + g * H + u + 4));
+                pre[g][0] = x0.x + b0.x; pre[g][1] = x0.y + b0.y; pre[g][2] = x0.z + b0.z; pre[g][3] = x0.w + b0.w;
+                pre[g][4] = x1.x + b1.x; pre[g][5] = x1.y + b1.y; pre[g][6] = x1.z + b1.z; pre[g][7] = x1.w + b1.w;
+            }
+            const float4 c0 = *reinterpret_cast<const float4*>(e.lstm_c + r_c + u);
+            const float4 c1 = *reinterpret_cast<const float4*>(e.lstm_c + r_c + u + 4);
+            cv[0] = c0.x; cv[1] = c0.y; cv[2] = c0.z; cv[3] = c0.w; cv[4] = c1.x; cv[5] = c1.y; cv[6] = c1.z; cv[7] = c1.w;
+        }
+        tmem_ld_wait();
+        if (ok) {
+            float ig[8], jg[8], fg[8], og[8], hv[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                ig[k] = fmaf(0.5f, fast_tanh(0.5f * (__uint_as_float(acc[0][k]) + pre[0][k])), 0.5f);
+                jg[k] = fast_tanh(__uint_as_float(acc[1][k]) + pre[1][k]);
+                fg[k] = fmaf(0.5f, fast_tanh(0.5f * (__uint_as_float(acc[2][k]) + pre[2][k] + e.forget_bias)), 0.5f);
+                og[k] = fmaf(0.5f, fast_tanh(0.5f * (__uint_as_float(acc[3][k]) + pre[3][k])), 0.5f);
+                cv[k] = fmaf(cv[k], fg[k], ig[k] * jg[k]);
+                hv[k] = fast_tanh(cv[k]) * og[k];
+            }
+            *reinterpret_cast<float4*>(e.lstm_c + r_c + u) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+            *reinterpret_cast<float4*>(e.lstm_c + r_c + u + 4) = make_float4(cv[4], cv[5], cv[6], cv[7]);
+            uint4 hp;
+            hp.x = pack_bf16(hv[0], hv[1]); hp.y = pack_bf16(hv[2], hv[3]); hp.z = pack_bf16(hv[4], hv[5]); hp.w = pack_bf16(hv[6], hv[7]);
+            *reinterpret_cast<uint4*>(e.lstm_h + static_cast<size_t>(row) * e.ld_lstm_h + u) = hp;
+            if (e.lstm_gates != nullptr) {
+                uint4 q;
+                q.x = pack_bf16(ig[0], ig[1]); q.y = pack_bf16(ig[2], ig[3]); q.z = pack_bf16(ig[4], ig[5]); q.w = pack_bf16(ig[6], ig[7]);
+                *reinterpret_cast<uint4*>(e.lstm_gates + r_g + u) = q;
+                q.x = pack_bf16(jg[0], jg[1]); q.y = pack_bf16(jg[2], jg[3]); q.z = pack_bf16(jg[4], jg[5]); q.w = pack_bf16(jg[6], jg[7]);
+                *reinterpret_cast<uint4*>(e.lstm_gates + r_g + H + u) = q;
+                q.x = pack_bf16(fg[0], fg[1]); q.y = pack_bf16(fg[2], fg[3]); q.z = pack_bf16(fg[4], fg[5]); q.w = pack_bf16(fg[6], fg[7]);
+                *reinterpret_cast<uint4*>(e.lstm_gates + r_g + 2 * H + u) = q;
+                q.x = pack_bf16(og[0], og[1]); q.y = pack_bf16(og[2], og[3]); q.z = pack_bf16(og[4], og[5]); q.w = pack_bf16(og[6], og[7]);
+                *reinterpret_cast<uint4*>(e.lstm_gates + r_g + 3 * H + u) = q;
+                *reinterpret_cast<float4*>(e.lstm_csave + r_c + u) = make_float4(cv[0], cv[1], cv[2], cv[3]);
+                *reinterpret_cast<float4*>(e.lstm_csave + r_c + u + 4) = make_float4(cv[4], cv[5], cv[6], cv[7]);
+            }
+        }
+    }
+}
+
 template <int BN, bool kPullB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -192,6 +266,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         mbar_init(&tmem_full_bar, 1);
         fence_mbar_init();
     }
+    // fused LSTM step: this CTA's 128 B rows are four 32-row boxes, rows g*H + 32*blockIdx.x ..
+    const bool lstm = (BN == 128) && !kPullB && epi.lstm_c != nullptr;
+    auto load_b = [&](uint8_t* b_dst, uint64_t* bar, int kcoord) {
+        if (lstm) {
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+                tma_load_2d(b_dst + g * 32 * 128, &tma_b, bar, kcoord, g * epi.lstm_H + static_cast<int>(blockIdx.x) * 32);
+        } else {
+            tma_load_2d(b_dst, &tma_b, bar, kcoord, n0);
+        }
+    };
     // B operand that does not depend on the previous kernel (weights): start streaming its first
     // stages now, under the previous kernel's tail; A (activations) follows after the wait.
     int pre = 0;
@@ -200,7 +285,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         if (warp == 0 && lane == 0) {
             for (int s = 0; s < pre; ++s) {
                 mbar_expect_tx(&full_bar[s], kStage);
-                tma_load_2d(smem + s * kStage + kBM * 128, &tma_b, &full_bar[s], (kb0 + s) * kBK, n0);
+                load_b(smem + s * kStage + kBM * 128, &full_bar[s], (kb0 + s) * kBK);
             }
         }
     }
@@ -231,7 +316,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                         mbar_wait(&empty_bar[s], ph ^ 1);
                         mbar_expect_tx(&full_bar[s], kStage);
                         tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
-                        tma_load_2d(b_dst, &tma_b, &full_bar[s], kb * kBK, n0);
+                        load_b(b_dst, &full_bar[s], kb * kBK);
                     }
                     if (++s == stages) { s = 0; ph ^= 1; }
                 }
@@ -305,7 +390,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         const uint32_t quad = warp & 3;       // TMEM lane quadrant this warp may read
         const int row = m0 + static_cast<int>(quad * 32 + lane);
         const uint32_t t_row = tmem_base + ((quad * 32u) << 16);
-        if constexpr (BN >= 32) {
+        if (lstm) {
+            lstm_step_epilogue(epi, t_row, row, M, static_cast<int>(blockIdx.x) * 32);
+        } else if constexpr (BN >= 32) {
 #pragma unroll 1
             for (int c = 0; c < BN; c += 32) {
                 if (n0 + c >= ((N + 7) & ~7)) break;   // warp-uniform
@@ -427,6 +514,8 @@ static int gemm_entry(const void* A, int lda, const void* B, int ldb, int M, int
     e.atomic_f32 = 0;
     e.split_stride = 0;
     e.b_static = epi->b_static;
+    e.lstm_gx = nullptr; e.ld_gx = 0; e.lstm_bias = nullptr; e.forget_bias = 0.f; e.lstm_c = nullptr; e.lstm_h = nullptr;
+    e.ld_lstm_h = 0; e.lstm_gates = nullptr; e.lstm_csave = nullptr; e.lstm_H = 0;
     // split-K for skinny problems with a long reduction (e.g. dh = dG Wh^T of the large-H LSTM:
     // M=64, N=4096, K=16384): partial sums are atomically added into the fp32 output
     int split_k = 1;
@@ -470,4 +559,27 @@ extern "C" int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int
 extern "C" int psb_gemm_bf16_pull(const void* A, int lda, const void* B_peer, int ldb, int M, int N, int K,
                                   const psb_epilogue_t* epi, int block_n, void* stream) {
     return gemm_entry(A, lda, B_peer, ldb, M, N, K, epi, block_n, stream, true);
+}
+
+
+extern "C" int psb_lstm_step_fwd(const void* h_prev, int ld_hp, const void* wh_t, int ld_w, int B, int H,
+                                 const float* gx, int ld_gx, const float* bias, float forget_bias, float* c,
+                                 void* h_out, int ld_h, void* gates_save, float* c_save, void* stream) {
+    using namespace psb;
+    if (!h_prev || !wh_t || !gx || !bias || !c || !h_out) return fail(PSB_ERR_ARG, "psb_lstm_step_fwd: null pointer argument");
+    if (B < 1 || H < 32 || H % 32) return fail(PSB_ERR_ARG, "psb_lstm_step_fwd: H must be a positive multiple of 32");
+    if (ld_hp % 8 || ld_w % 8 || ld_h % 8 || ld_gx % 4) return fail(PSB_ERR_ARG, "psb_lstm_step_fwd: leading dimensions must be 16-byte multiples");
+    if ((gates_save != nullptr) != (c_save != nullptr)) return fail(PSB_ERR_ARG, "psb_lstm_step_fwd: gates_save and c_save go together");
+    const CUtensorMap* ta = tensor_map_bf16_2d(h_prev, B, H, ld_hp, kBM);
+    if (!ta) return PSB_ERR_DRIVER;
+    const CUtensorMap* tb = tensor_map_bf16_2d(wh_t, 4 * static_cast<uint64_t>(H), H, ld_w, 32);   // 32-row boxes: one gate block each
+    if (!tb) return PSB_ERR_DRIVER;
+    EpiArgs e = {};
+    e.alpha = 1.0f;
+    e.b_static = 1;
+    e.lstm_gx = gx; e.ld_gx = ld_gx; e.lstm_bias = bias; e.forget_bias = forget_bias; e.lstm_c = c;
+    e.lstm_h = static_cast<__nv_bfloat16*>(h_out); e.ld_lstm_h = ld_h;
+    e.lstm_gates = static_cast<__nv_bfloat16*>(gates_save); e.lstm_csave = c_save; e.lstm_H = H;
+    // N = 128 * (H / 32): every CTA owns 32 hidden units = 4 x 32 gate columns
+    return launch_gemm<128, false>(ta, tb, B, 4 * H, H, e, static_cast<cudaStream_t>(stream), nullptr, 0, 1);
 }

@@ -663,10 +663,10 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     cfg.blockDim = dim3(kLstmThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = static_cast<cudaStream_t>(stream);
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
+    cudaLaunchAttribute pdl[1];
+    pdl[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    pdl[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = pdl;
     cfg.numAttrs = 1;
     PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_bwd_kernel, a));
     return after_launch("lstm_bwd");

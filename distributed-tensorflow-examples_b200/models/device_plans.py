@@ -285,6 +285,8 @@ class ScaledLstmPlan(DevicePlan):
         self.split_k = 2 if big else 1
         self.bn_fwd = 128 if big else 0
         self.bn_bwd = 64 if big else 0
+        # forward timestep = ONE kernel (recurrent GEMM with the cell pointwise in its epilogue)
+        self.fuse_fwd = (H % 32 == 0) and int(__import__('os').environ.get('PSB_SCALED_FUSE', '1')) == 1
         self.dh_rec = torch.zeros(self.split_k, B, H, device=dev)
         self.dc = torch.zeros(B, H, device=dev)
         self.dY = torch.zeros(TB, H, device=dev) if L > 1 else None  # gradient arriving from the layer above
@@ -312,6 +314,12 @@ class ScaledLstmPlan(DevicePlan):
             self.c.zero_()
             for t in range(T):
                 hprev = self.h0 if t == 0 else self._rows(self.Hall[l], t - 1)
+                if self.fuse_fwd:
+                    K.lstm_step_fwd(hprev, wh_t, self.gx[t * B:(t + 1) * B], bias, 1.0, self.c,
+                                    self._rows(self.Hall[l], t),
+                                    self.gates[l][t * B:(t + 1) * B] if train else None,
+                                    self.c_all[l][t * B:(t + 1) * B] if train else None)
+                    continue
                 K.gemm(hprev, wh_t, out_f32=self.gh, block_n=self.bn_fwd, b_static=True)
                 K.lstm_cell_fwd(self.gx[t * B:(t + 1) * B], self.gh, bias, 1.0, self.c, self._rows(self.Hall[l], t),
                                 self.gates[l][t * B:(t + 1) * B] if train else None,

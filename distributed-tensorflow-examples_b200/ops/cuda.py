@@ -299,3 +299,17 @@ def lstm_cell_bwd(dh_rec: Optional[torch.Tensor], dy: Optional[torch.Tensor], ga
 def transpose_bf16(src: BMat, dst: BMat) -> None:
     check(_lib.lib().psb_transpose_bf16(src.ptr, src.ld, src.rows, src.cols, dst.ptr, dst.ld,
                                         current_stream_ptr()), "psb_transpose_bf16")
+
+
+_lib.register_signature("psb_lstm_step_fwd", [c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                                              c_void_p, c_float, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p])
+
+
+def lstm_step_fwd(h_prev: BMat, wh_t: BMat, gx: torch.Tensor, bias: torch.Tensor, forget_bias: float,
+                  c: torch.Tensor, h_out: BMat, gates_save: Optional[torch.Tensor] = None,
+                  c_save: Optional[torch.Tensor] = None) -> None:
+    """Recurrent GEMM + cell pointwise of one timestep fused in one kernel (large-H path)."""
+    B, H = c.shape
+    check(_lib.lib().psb_lstm_step_fwd(h_prev.ptr, h_prev.ld, wh_t.ptr, wh_t.ld, B, H, gx.data_ptr(), gx.stride(0),
+                                       bias.data_ptr(), float(forget_bias), c.data_ptr(), h_out.ptr, h_out.ld,
+                                       _ptr(gates_save), _ptr(c_save), current_stream_ptr()), "psb_lstm_step_fwd")

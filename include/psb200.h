@@ -124,6 +124,14 @@ int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const
  * split-K outputs of the dh GEMM) + dy (either may be NULL), dc fp32 [B,H] updated in place, dg bf16
  * [B, ld_dg] = gate gradients, dbias fp32 [4H] += column sums (atomic).
  * ref: rnn.BasicLSTMCell / static_rnn, lstm:50-52, scaled per BASELINE.json config #4. */
+/* One forward timestep of the large-H LSTM in ONE kernel: gates = h_prev Wh (tcgen05 GEMM, every
+ * CTA gathers the i/j/f/o rows of its 32 hidden units with four 32-row TMA boxes) + gx + bias,
+ * then the cell pointwise in the epilogue.  h_prev bf16 [B, ld_hp], wh_t bf16 [4H, ld_w] (the
+ * recurrent half of kernel^T), gx fp32 [B, ld_gx], c fp32 [B,H] in/out, h_out bf16 [B, ld_h];
+ * optional saves as in psb_lstm_cell_fwd.  H must be a multiple of 32. */
+int psb_lstm_step_fwd(const void* h_prev, int ld_hp, const void* wh_t, int ld_w, int B, int H,
+                      const float* gx, int ld_gx, const float* bias, float forget_bias, float* c,
+                      void* h_out, int ld_h, void* gates_save, float* c_save, void* stream);
 int psb_lstm_cell_fwd(const float* gx, int ld_gx, const float* gh, int ld_gh, const float* bias,
                       float forget_bias, float* c, void* h_out, int ld_h, void* gates_save,
                       float* c_save, int B, int H, void* stream);
