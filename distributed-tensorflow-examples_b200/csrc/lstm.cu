@@ -39,8 +39,7 @@ constexpr int kMmaWarps = 4;           // backward: issuing warps (a thread sust
 constexpr int kLstmThreads = kPW + 32 * kMmaWarps;
 constexpr int kFwdMmaWarps = 4;        // forward: one issuing warp per gate block
 constexpr int kFwdThreads = kPW + 32 * kFwdMmaWarps;
-constexpr int kFwdKB = 3;            // k-blocks of 64 covering I+H <= 160 (+pad)
-constexpr int kFwdBSmem = kFwdKB * kNB * 128;      // 6144 >= 16 x 160 x 2: the [x_t, h_{t-1}] operand
+constexpr int kFwdBSmem = 6144;      // >= 16 x 160 x 2 bytes: the [x_t, h_{t-1}] operand tile
 constexpr int kFwdKMax = 160;        // I + H <= 160: 80 TMEM columns per gate block
 // [x_t, h_{t-1}] operand, MN-major without swizzle: element (b, k) of the 16 x 160 tile at
 //   (b>>3)*kXhSbo + (k>>3)*128 + (k&7)*16 + (b&7)*2   — a thread's 8 batch rows of one k are 16 bytes
@@ -50,8 +49,7 @@ constexpr uint32_t kXhSbo = (kFwdKMax / 8) * 128;
 // four interleaved accumulators in the backward kernel.
 constexpr uint32_t kFwdAcc = 0;      // TMEM columns [0, 64): gate accumulators (columns 64..127 unused)
 constexpr uint32_t kFwdW = 128;      // TMEM columns [128, 128 + 4*80): the cell kernel (A operand)
-constexpr int kBwdKB = 8;            // 4H / 64
-constexpr int kBwdBSmem = kBwdKB * kNB * 128;      // 16384: the dG_t operand
+constexpr int kBwdBSmem = 16 * 4 * kH * 2;      // 16384: the dG_t operand tile (16 x 512 bf16)
 constexpr int kStageRow = 144;                 // 128 data bytes + 16 pad: conflict-free 16-byte column writes
 constexpr int kFwdStage = kH * kStageRow;      // h rows x (4 steps x 16 batch) bf16, double-buffered
 constexpr int kBwdStage = 4 * kH * kStageRow;  // dG rows x (4 steps x 16 batch) bf16, double-buffered
@@ -59,21 +57,9 @@ constexpr uint32_t kBwdW = 64;       // TMEM columns [64, 64 + 256): Wh (A opera
 
 __device__ __forceinline__ float sigmoid_t(float x) { return fmaf(0.5f, fast_tanh(0.5f * x), 0.5f); }
 
-// byte offset of element (row, k) inside a K-major 128B-swizzled operand made of k-blocks of
-// `rows` rows x 128 bytes
-__device__ __forceinline__ uint32_t swz_off(int rows, int row, int k) {
-    const int kb = k >> 6, kk = k & 63;
-    return static_cast<uint32_t>(kb * rows * 128 + row * 128 + ((((kk >> 3) ^ (row & 7)) << 4)) + ((kk & 7) << 1));
-}
-
 __device__ __forceinline__ uint32_t xh_off(int b, int k) {
     return static_cast<uint32_t>((b >> 3) * kXhSbo + (k >> 3) * 128 + (k & 7) * 16 + (b & 7) * 2);
 }
-
-__device__ __forceinline__ void sts_bf16(uint8_t* base, uint32_t off, uint32_t packed_lo16) {
-    *reinterpret_cast<uint16_t*>(base + off) = static_cast<uint16_t>(packed_lo16);
-}
-
 
 // Column order shared by xh_t and dg_t (the two operands of the weight-gradient GEMM):
 //   col(cta, t, b) = (cta * T + t) * 16 + b
