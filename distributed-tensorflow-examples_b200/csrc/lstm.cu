@@ -612,13 +612,8 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
         attr = true;
     }
     const int ctas = (B + kNB - 1) / kNB;
-    if (xh_t != nullptr) {
-        if (ld_xht < ctas * T * kNB)
-            return fail(PSB_ERR_ARG, "psb_lstm_fwd: xh_t needs %d columns (ceil(B/16)*T*16)", ctas * T * kNB);
-        lstm_xt_kernel<<<dim3(T, ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, B, T, I, a.xh_t, ld_xht);
-        int rc = after_launch("lstm_xt");
-        if (rc != PSB_OK) return rc;
-    }
+    if (xh_t != nullptr && ld_xht < ctas * T * kNB)
+        return fail(PSB_ERR_ARG, "psb_lstm_fwd: xh_t needs %d columns (ceil(B/16)*T*16)", ctas * T * kNB);
     lstm_fwd_kernel<<<ctas, kFwdThreads, smem, static_cast<cudaStream_t>(stream)>>>(a);
     return after_launch("lstm_fwd");
 }
@@ -656,4 +651,16 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     cfg.numAttrs = 1;
     PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_bwd_kernel, a));
     return after_launch("lstm_bwd");
+}
+
+
+// The x rows of xh_t (rows 0..I-1, same column order as psb_lstm_fwd's h rows).  Separate entry
+// point so that it can run on another stream: only the weight-gradient GEMM needs it.
+extern "C" int psb_lstm_xt(const float* x, int B, int T, int I, void* xh_t, int ld_xht, void* stream) {
+    using namespace psb;
+    const int ctas = (B + kNB - 1) / kNB;
+    if (!x || !xh_t || B < 1 || T < 1 || I < 1) return fail(PSB_ERR_ARG, "psb_lstm_xt: bad argument");
+    if (ld_xht % 8 || ld_xht < ctas * T * kNB) return fail(PSB_ERR_ARG, "psb_lstm_xt: xh_t needs ceil(B/16)*T*16 columns, ld%%8==0");
+    lstm_xt_kernel<<<dim3(T, ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, B, T, I, static_cast<__nv_bfloat16*>(xh_t), ld_xht);
+    return after_launch("lstm_xt");
 }

@@ -236,6 +236,10 @@ class LstmPlan(DevicePlan):
         s, n = self.store, self._name
         _, w_ptr = self._kernel_ptrs()
         s.zero_grads()
+        # the transposed inputs are only read by the last GEMM of the step: side stream
+        self._fork()
+        with torch.cuda.stream(self.side):
+            K.lstm_xt(self.inputs["x"], self.saved)
         self.forward(train=True)
         K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
                             self.dlogits_t, s.grad(n("out_b")), self.correct)

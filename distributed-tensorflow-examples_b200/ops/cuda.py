@@ -132,6 +132,7 @@ from ctypes import c_float, c_int, c_void_p  # noqa: E402
 _lib.register_signature("psb_lstm_fwd", [c_void_p, c_void_p, c_int, c_void_p, c_float, c_int, c_int,
                                          c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p,
                                          c_void_p, c_void_p, c_int, c_void_p])
+_lib.register_signature("psb_lstm_xt", [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_lstm_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int,
                                          c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p])
 _lib.register_signature("psb_cast_transpose", [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
@@ -196,6 +197,13 @@ def lstm_fwd(x: torch.Tensor, wt: BMat, bias: torch.Tensor, forget_bias: float,
         saved.gates.data_ptr() if saved else None, saved.c_all.data_ptr() if saved else None,
         saved.xh_t.ptr if saved else None, saved.xh_t.ld if saved else 0,
         current_stream_ptr()), "psb_lstm_fwd")
+
+
+def lstm_xt(x: torch.Tensor, saved: "LstmSaved") -> None:
+    """Input rows of ``saved.xh_t`` (needed only by the weight-gradient GEMM; any stream)."""
+    B, T, I = x.shape
+    check(_lib.lib().psb_lstm_xt(x.data_ptr(), B, T, I, saved.xh_t.ptr, saved.xh_t.ld, current_stream_ptr()),
+          "psb_lstm_xt")
 
 
 def lstm_bwd(w: BMat, dh_last: torch.Tensor, saved: LstmSaved, dbias: torch.Tensor,

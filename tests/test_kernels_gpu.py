@@ -25,6 +25,7 @@ def test_lstm_fwd_bwd(B, T, I):
     Wt = K_.BMat.from_tensor(kernel.t().contiguous())   # [4H, I+H]
     h_last, h_last_t = K_.BMat(B, H), K_.BMat(H, B)
     saved = K_.LstmSaved(B, T, I, H)
+    K_.lstm_xt(x, saved)
     K_.lstm_fwd(x, Wt, bias, 1.0, h_last, h_last_t, saved)
     torch.cuda.synchronize()
 
