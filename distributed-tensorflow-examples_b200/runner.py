@@ -124,6 +124,7 @@ def run_worker_cpu(model_name: str, flags: Flags, cluster: ClusterSpec, server: 
         result.update(local_steps=local_step, global_step=step, restored_from=sv.restored_from)
         if flags.sync:
             sv.request_stop()
+        sv.final_checkpoint()       # while the ps tasks still hold the variables
         # Signal to ps shards that we are done
         store.enqueue_done(flags.workers)
     sv.stop()

@@ -46,6 +46,7 @@ class Supervisor:
         self.restored_from: Optional[str] = None
         self.last_saved: Optional[str] = None
         self._save_lock = threading.Lock()
+        self._final_done = False
 
     # ---- stop protocol -------------------------------------------------------------
     def should_stop(self) -> bool:
@@ -158,13 +159,22 @@ class Supervisor:
             self.request_stop()
             raise
         finally:
-            if self.is_chief and self.save_model_secs and not getattr(self, "_skip_final", False):
-                try:
-                    self._stop.set()
-                    for t in self._threads:
-                        if t.name == "SVTimerCheckpointThread":
-                            t.join(timeout=10.0)
-                    self.save_checkpoint()
-                except Exception as e:
-                    print("final checkpoint failed: %r" % (e,), flush=True)
+            self.final_checkpoint()
             self.stop()
+
+    def final_checkpoint(self) -> Optional[str]:
+        """Chief only, once: stop the checkpoint timer and save the current state.  The worker
+        loop calls it BEFORE it enqueues its done token, because the ps tasks exit as soon as the
+        last token arrives and the variables go with them."""
+        if not self.is_chief or not self.save_model_secs or self._final_done:
+            return None
+        self._final_done = True
+        try:
+            self._stop.set()
+            for t in self._threads:
+                if t.name == "SVTimerCheckpointThread":
+                    t.join(timeout=10.0)
+            return self.save_checkpoint()
+        except Exception as e:
+            print("final checkpoint failed: %r" % (e,), flush=True)
+            return None
