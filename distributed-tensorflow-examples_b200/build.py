@@ -22,7 +22,7 @@ LIB = os.path.join(HERE, "lib")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
 KERNEL_SOURCES = ["lib.cu", "gemm.cu", "lstm.cu", "losses.cu", "push.cu", "peer.cu", "lstm_cell.cu"]
-PS_SOURCES = ["ps_server.cpp"]
+PS_SOURCES = ["ps_server.cpp", "tf_bundle.cpp"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math" if False else "-DNDEBUG"]

@@ -5,8 +5,11 @@
 a ``checkpoint`` state file, keep the newest five, and save every global variable under its
 graph name (``Variable``, ``Variable_1`` .., ``Variable/RMSProp`` ..,
 ``beta1_power`` .., ``rnn/basic_lstm_cell/kernel``).  File names, the state-file syntax and the
-key set are reproduced; the tensor bundle itself is a self-describing container (JSON index +
-raw little-endian data) because TF's SSTable bundle cannot be validated without TensorFlow.
+key set are reproduced.  Two bundle formats: ``"psb200"`` (default; JSON index + raw
+little-endian data, self-describing and diff-able) and ``"tf"`` (TensorFlow's own V2 bundle:
+string-table ``.index`` + raw ``.data`` shard, written natively by ``csrc/tf_bundle.cpp``).
+``restore``/``list_variables`` recognise either.  ``.meta`` is always this framework's JSON
+placement table: a TF ``MetaGraphDef`` describes a TF graph, which does not exist here.
 """
 from __future__ import annotations
 
@@ -57,14 +60,24 @@ def latest_checkpoint(model_dir: str) -> Optional[str]:
 
 
 class Saver:
-    def __init__(self, max_to_keep: int = 5):
+    def __init__(self, max_to_keep: int = 5, bundle_format: str = "psb200"):
+        if bundle_format not in ("psb200", "tf"):
+            raise ValueError("bundle_format must be 'psb200' or 'tf'")
         self.max_to_keep = max_to_keep
+        self.bundle_format = bundle_format
 
     def save(self, values: Dict[str, torch.Tensor], model_dir: str, global_step: int,
              meta: Optional[dict] = None, basename: str = "model.ckpt") -> str:
         os.makedirs(model_dir, exist_ok=True)
         name = "%s-%d" % (basename, int(global_step))
         prefix = os.path.join(model_dir, name)
+        if self.bundle_format == "tf":
+            from . import tf_bundle
+            tf_bundle.write_bundle(prefix, values)
+            with open(prefix + ".meta", "w") as f:
+                json.dump(meta or {}, f)
+            self._update_state(model_dir, name)
+            return prefix
         index, offset = {}, 0
         tmp = prefix + ".data-00000-of-00001.tmp"
         with open(tmp, "wb") as f:
@@ -103,6 +116,9 @@ class Saver:
 
     @staticmethod
     def restore(prefix: str) -> Dict[str, torch.Tensor]:
+        from . import tf_bundle
+        if tf_bundle.is_tf_bundle(prefix):
+            return tf_bundle.read_bundle(prefix)
         with open(prefix + ".index") as f:
             idx = json.load(f)
         out = {}
@@ -117,6 +133,9 @@ class Saver:
     @staticmethod
     def list_variables(prefix: str) -> Dict[str, List[int]]:
         """``tf.train.list_variables``: name -> shape."""
+        from . import tf_bundle
+        if tf_bundle.is_tf_bundle(prefix):
+            return tf_bundle.list_variables(prefix)
         with open(prefix + ".index") as f:
             idx = json.load(f)
         return {k: e["shape"] for k, e in idx["tensors"].items()}

@@ -54,6 +54,7 @@ class Flags:
     ps_wait_timeout: float = 0.0       # 0 -> ps waits forever for done tokens (reference)
     recovery_wait_secs: float = 1.0    # non-chief polling period (TF default is 30 s)
     batch_size: int = 0                # 0 -> the script's module constant
+    checkpoint_format: str = "psb200"  # bundle written by the chief: "psb200" (JSON index) | "tf" (TF V2 bundle)
     extra: List[str] = field(default_factory=list)
 
     def ps_list(self) -> List[str]:
@@ -101,6 +102,8 @@ def parse_flags(argv: Optional[Sequence[str]] = None, prog: Optional[str] = None
     fl.extra = list(extra)
     if fl.backend not in ("cpu", "nvl"):
         raise SystemExit("--backend must be 'cpu' or 'nvl'")
+    if fl.checkpoint_format not in ("psb200", "tf"):
+        raise SystemExit("--checkpoint_format must be 'psb200' or 'tf'")
     if fl.gan_update not in ("simultaneous", "alternating"):
         raise SystemExit("--gan_update must be 'simultaneous' or 'alternating'")
     return fl

@@ -87,7 +87,7 @@ def run_worker_cpu(model_name: str, flags: Flags, cluster: ClusterSpec, server: 
     store = TcpStore(cluster, registry, model, num_workers=flags.workers)
     _ = device_filters(flags.task_index)        # a worker only ever opens connections to ps tasks
     sv = Supervisor(is_chief=(flags.task_index == 0), logdir=flags.model_dir, store=store,
-                    registry=registry, model=model, saver=Saver(), save_model_secs=flags.save_model_secs,
+                    registry=registry, model=model, saver=Saver(bundle_format=flags.checkpoint_format), save_model_secs=flags.save_model_secs,
                     recovery_wait_secs=flags.recovery_wait_secs, seed=flags.seed, sync=flags.sync,
                     replicas_to_aggregate=flags.replicas_to_aggregate, reinit_on_join=flags.reinit_on_join)
     mnist = read_data_sets(flags.data_dir, one_hot=True, synthetic=flags.synthetic, seed=flags.seed + flags.task_index)
@@ -168,7 +168,7 @@ def run_worker_nvl(model_name: str, flags: Flags, cluster: ClusterSpec, server: 
         dist.broadcast_object_list(box, src=0, group=group)
         values = box[0]
     tr.initialize(values)
-    saver = Saver()
+    saver = Saver(bundle_format=flags.checkpoint_format)
     last_save = [0.0]
 
     def maybe_checkpoint(force=False):

@@ -115,3 +115,24 @@ def test_launcher_runs_a_whole_cluster(tmp_path):
                       model_dir=str(tmp_path / "m"), quiet=True, timeout=120)
     assert rc == 0, logs
     assert "ps 0: quitting" in logs["ps:0"] and "Total Time:" in logs["worker:1"]
+
+
+def test_tf_bundle_checkpoints_resume(tmp_path):
+    """--checkpoint_format=tf: the chief writes TensorFlow V2 bundles and a restarted chief resumes from one."""
+    from psb200 import tf_bundle
+    from psb200.checkpoint import latest_checkpoint
+    from psb200.launch import launch
+    model_dir = str(tmp_path / "m")
+    extra = ["--synthetic", "--save_model_secs=1", "--checkpoint_format=tf"]
+    rc, logs = launch("lstm", workers=2, ps=1, backend="cpu", extra=extra + ["--num_steps=8"],
+                      model_dir=model_dir, quiet=True, timeout=120)
+    assert rc == 0, logs
+    latest = latest_checkpoint(model_dir)
+    assert latest is not None and tf_bundle.is_tf_bundle(latest)
+    saved = int(tf_bundle.read_bundle(latest)["Variable_2"])
+    assert saved >= 8
+    rc, logs = launch("lstm", workers=2, ps=1, backend="cpu", extra=extra + ["--num_steps=%d" % (saved + 4)],
+                      model_dir=model_dir, quiet=True, timeout=120)
+    assert rc == 0, logs
+    steps = _global_steps(logs["worker:0"]) + _global_steps(logs["worker:1"])
+    assert min(steps) > saved - 1 and max(steps) >= saved + 4
