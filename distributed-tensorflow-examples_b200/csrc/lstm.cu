@@ -335,7 +335,28 @@ struct LstmBwdArgs {
     int ld_dgt;
     float* dbias;                // [4H] fp32, += sum over CTAs in CTA order
     float* dbias_part;           // scratch [gridDim.x][4H] fp32 + 1 counter word at the end
+    psb_lstm_head_t head;        // head.w_out != nullptr: classifier head fused into the prologue
 };
+
+// Per-CTA partials of the fused head: dW_out [H][16], db_out [16], loss, correct.
+constexpr int kHeadC = 16;
+constexpr int kHeadPart = kH * kHeadC + kHeadC + 2;
+
+__device__ __forceinline__ float grp16_max(float v) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float grp16_sum(float v) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int grp16_min(int v) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
 
 __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a) {
     extern __shared__ uint8_t smem_raw[];
@@ -417,9 +438,86 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         float dh[kHB], dc[kHB], c_new[kHB], c_old[kHB];
         float dbs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int b = 0; b < kHB; ++b) {
-            dh[b] = (b0 + bb + b < a.B) ? a.dh_last[static_cast<size_t>(b0 + bb + b) * a.ld_dh + u] : 0.0f;
-            dc[b] = 0.0f;
+        for (int b = 0; b < kHB; ++b) dc[b] = 0.0f;
+        if (a.head.w_out != nullptr) {
+            // ---- fused classifier head for this CTA's 16 rows (lstm:53,92-94 and their gradients):
+            // logits = h_T W + b, softmax cross-entropy, dlogits, dh_T = dlogits W^T, and this CTA's
+            // partial dW = h_T^T dlogits / db / loss / correct (summed in CTA order by the last CTA).
+            // The staging buffers are free until the first timestep: they hold the temporaries.
+            const psb_lstm_head_t& hd = a.head;
+            const int C = hd.C;
+            float* sh = reinterpret_cast<float*>(sStage);        // [16][129] h_T
+            float* sW = sh + kNB * 129;                          // [128][17] W_out
+            float* sdl = sW + kH * 17;                           // [16][17]  dlogits
+            float* sred = sdl + kNB * 17;                        // [16][2]   loss, correct per row
+            const __nv_bfloat16* hl = static_cast<const __nv_bfloat16*>(hd.h_last);
+            const __nv_bfloat16* wo = static_cast<const __nv_bfloat16*>(hd.w_out);
+            for (int e = static_cast<int>(tid); e < kNB * kH; e += kPW) {
+                const int b = e >> 7, j = e & 127;
+                sh[b * 129 + j] = (b0 + b < a.B) ? __bfloat162float(hl[static_cast<size_t>(b0 + b) * hd.ld_h + j]) : 0.0f;
+            }
+            for (int e = static_cast<int>(tid); e < kH * kHeadC; e += kPW) {
+                const int j = e >> 4, k = e & 15;
+                sW[j * 17 + k] = (k < C) ? __bfloat162float(wo[static_cast<size_t>(j) * hd.ld_wo + k]) : 0.0f;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+            {
+                const int b = static_cast<int>(tid >> 4), k = static_cast<int>(tid & 15);
+                const bool in_c = k < C, valid = in_c && (b0 + b < a.B);
+                float z = 0.0f;
+#pragma unroll 8
+                for (int j = 0; j < kH; ++j) z = fmaf(sh[b * 129 + j], sW[j * 17 + k], z);
+                if (in_c) z += hd.b_out[k];
+                const float y = valid ? hd.labels[static_cast<size_t>(b0 + b) * hd.ld_l + k] : 0.0f;
+                const float zz = in_c ? z : -INFINITY;
+                const float mx = grp16_max(zz);
+                const int am = grp16_min((in_c && zz == mx) ? k : 99);      // first maximum, like the loss kernel
+                const float ymax = grp16_max(in_c ? y : -INFINITY);
+                const int ay = grp16_min((in_c && y == ymax) ? k : 99);
+                const float ysum = grp16_sum(y);
+                const float se = grp16_sum(in_c ? __expf(zz - mx) : 0.0f);
+                const float lse = mx + __logf(se);
+                const float g = valid ? (__expf(zz - lse) * ysum - y) / static_cast<float>(a.B) : 0.0f;
+                const float lrow = grp16_sum(valid ? -y * (zz - lse) : 0.0f);
+                sdl[b * 17 + k] = g;
+                if (valid && hd.logits != nullptr) hd.logits[static_cast<size_t>(b0 + b) * hd.ld_logits + k] = z;
+                if (k == 0) {
+                    const bool row = b0 + b < a.B;
+                    sred[2 * b] = row ? lrow : 0.0f;
+                    sred[2 * b + 1] = (row && am == ay) ? 1.0f : 0.0f;
+                }
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");
+#pragma unroll
+            for (int b = 0; b < kHB; ++b) {
+                float acc = 0.0f;
+#pragma unroll
+                for (int k = 0; k < kHeadC; ++k) acc = fmaf(sdl[(bb + b) * 17 + k], sW[u * 17 + k], acc);
+                dh[b] = acc;
+            }
+            float* part = hd.scratch + static_cast<size_t>(blockIdx.x) * kHeadPart;
+#pragma unroll
+            for (int kk = 0; kk < kHeadC / 2; ++kk) {
+                const int k = half * (kHeadC / 2) + kk;
+                float acc = 0.0f;
+#pragma unroll
+                for (int b = 0; b < kNB; ++b) acc = fmaf(sh[b * 129 + u], sdl[b * 17 + k], acc);
+                part[u * kHeadC + k] = acc;
+            }
+            if (tid < kHeadC) {
+                float acc = 0.0f;
+                for (int b = 0; b < kNB; ++b) acc += sdl[b * 17 + tid];
+                part[kH * kHeadC + tid] = acc;
+            } else if (tid < kHeadC + 2) {
+                float acc = 0.0f;
+                for (int b = 0; b < kNB; ++b) acc += sred[2 * b + (tid - kHeadC)];
+                part[kH * kHeadC + tid] = acc;
+            }
+            asm volatile("bar.sync 1, 256;" ::: "memory");      // temporaries dead: staging may be written
+        } else {
+#pragma unroll
+            for (int b = 0; b < kHB; ++b)
+                dh[b] = (b0 + bb + b < a.B) ? a.dh_last[static_cast<size_t>(b0 + bb + b) * a.ld_dh + u] : 0.0f;
         }
         // saved activations of the last step
         uint4 gq[4];
@@ -552,7 +650,7 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         flush_group(sStage, 4 * kH, a.dg_t, a.ld_dgt, static_cast<size_t>(blockIdx.x) * a.T * kNB,
                     a.T < 4 ? a.T : 4, warp, lane);
     }
-    if (a.dbias != nullptr) {
+    if (a.dbias_part != nullptr) {
         // the last CTA to get here adds the per-CTA partials in CTA order
         __shared__ bool last;
         unsigned int* counter = reinterpret_cast<unsigned int*>(a.dbias_part + static_cast<size_t>(gridDim.x) * 4 * kH);
@@ -563,11 +661,25 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         __syncthreads();
         if (last) {
             __threadfence();
-            for (int i = tid; i < 4 * kH; i += blockDim.x) {
+            for (int i = tid; a.dbias != nullptr && i < 4 * kH; i += blockDim.x) {
                 float s = 0.0f;
                 for (unsigned int cta = 0; cta < gridDim.x; ++cta)
                     s += *reinterpret_cast<volatile float*>(a.dbias_part + static_cast<size_t>(cta) * 4 * kH + i);
                 a.dbias[i] += s;
+            }
+            if (a.head.w_out != nullptr) {
+                const psb_lstm_head_t& hd = a.head;
+                for (int i = tid; i < kHeadPart; i += blockDim.x) {
+                    const int k = i & (kHeadC - 1);
+                    if (i < kH * kHeadC + kHeadC && k >= hd.C) continue;
+                    float s = 0.0f;
+                    for (unsigned int cta = 0; cta < gridDim.x; ++cta)
+                        s += *reinterpret_cast<volatile float*>(hd.scratch + static_cast<size_t>(cta) * kHeadPart + i);
+                    if (i < kH * kHeadC) { if (hd.d_w_out != nullptr) hd.d_w_out[static_cast<size_t>(i >> 4) * hd.ld_dwo + k] += s; }
+                    else if (i < kH * kHeadC + kHeadC) { if (hd.d_b_out != nullptr) hd.d_b_out[k] += s; }
+                    else if (i == kH * kHeadC + kHeadC) { if (hd.loss != nullptr) *hd.loss = s / static_cast<float>(a.B); }
+                    else if (hd.correct != nullptr) *hd.correct = s;
+                }
             }
             if (tid == 0) *counter = 0;
         }
@@ -618,12 +730,18 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
     return after_launch("lstm_fwd");
 }
 
-extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const void* gates,
-                            const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
-                            float* dbias, float* dbias_scratch, void* stream) {
+static int lstm_bwd_launch(const void* w, int ld_w, const float* dh_last, int ld_dh, const psb_lstm_head_t* head,
+                           const void* gates, const float* c_all, int B, int T, int I, int H, void* dg_t,
+                           int ld_dgt, float* dbias, float* dbias_scratch, void* stream) {
     using namespace psb;
     if (H != kH) return fail(PSB_ERR_ARG, "psb_lstm_bwd: this kernel is built for H=128 (got %d)", H);
-    if (!w || !dh_last || !gates || !c_all || B < 1 || T < 1) return fail(PSB_ERR_ARG, "psb_lstm_bwd: bad argument");
+    if (!w || (!dh_last && !head) || !gates || !c_all || B < 1 || T < 1) return fail(PSB_ERR_ARG, "psb_lstm_bwd: bad argument");
+    if (head != nullptr) {
+        if (!head->h_last || !head->w_out || !head->b_out || !head->labels || !head->scratch || !dbias_scratch)
+            return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: h_last, w_out, b_out, labels, scratch and dbias_scratch are required");
+        if (head->C < 1 || head->C > kHeadC || head->ld_wo < head->C || head->ld_h < kH)
+            return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: 1 <= C <= 16, ld_wo >= C, ld_h >= H");
+    }
     if (ld_w % 8 || ld_w < 4 * H) return fail(PSB_ERR_ARG, "psb_lstm_bwd: ld_w must be a multiple of 8 covering 4H");
     if (dg_t && (ld_dgt % 8 || ld_dgt < ((B + kNB - 1) / kNB) * T * kNB))
         return fail(PSB_ERR_ARG, "psb_lstm_bwd: dg_t needs ld_dgt%%8==0 and ceil(B/16)*T*16 columns");
@@ -633,6 +751,8 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     a.gates = static_cast<const uint4*>(gates); a.c_all = reinterpret_cast<const float4*>(c_all);
     a.B = B; a.T = T; a.I = I;
     a.dg_t = static_cast<__nv_bfloat16*>(dg_t); a.ld_dgt = ld_dgt; a.dbias = dbias; a.dbias_part = dbias_scratch;
+    if (head != nullptr) a.head = *head;
+    else memset(&a.head, 0, sizeof(a.head));
     const size_t smem = kBwdBSmem + 2 * kBwdStage + 1024;
     static bool attr = false;
     if (!attr) {
@@ -651,6 +771,25 @@ extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int l
     cfg.numAttrs = 1;
     PSB_CUDA_OK(cudaLaunchKernelEx(&cfg, lstm_bwd_kernel, a));
     return after_launch("lstm_bwd");
+}
+
+extern "C" int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const void* gates,
+                            const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
+                            float* dbias, float* dbias_scratch, void* stream) {
+    return lstm_bwd_launch(w, ld_w, dh_last, ld_dh, nullptr, gates, c_all, B, T, I, H, dg_t, ld_dgt, dbias,
+                           dbias_scratch, stream);
+}
+
+extern "C" size_t psb_lstm_head_scratch_floats(int B) {
+    return static_cast<size_t>((B + psb::kNB - 1) / psb::kNB) * psb::kHeadPart;
+}
+
+extern "C" int psb_lstm_bwd_head(const void* w, int ld_w, const psb_lstm_head_t* head, const void* gates,
+                                 const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
+                                 float* dbias, float* dbias_scratch, void* stream) {
+    if (!head) return psb::fail(psb::PSB_ERR_ARG, "psb_lstm_bwd_head: head is required");
+    return lstm_bwd_launch(w, ld_w, nullptr, 0, head, gates, c_all, B, T, I, H, dg_t, ld_dgt, dbias,
+                           dbias_scratch, stream);
 }
 
 

@@ -188,11 +188,15 @@ class GanPlan(DevicePlan):
 
 
 class LstmPlan(DevicePlan):
-    """``lstm:49-53,89-100`` — persistent LSTM forward kernel, head GEMM, fused softmax-CE,
-    head wgrad/dgrad GEMMs, persistent BPTT kernel, one big wgrad GEMM for the cell kernel."""
+    """``lstm:49-53,89-100`` — persistent LSTM forward kernel, persistent BPTT kernel with the
+    classifier head (logits, softmax-CE, head gradients) fused into its prologue, one big wgrad
+    GEMM for the cell kernel.  ``fuse_head=False`` runs the head as separate kernels instead (head
+    GEMM, softmax-CE kernel, head wgrad/dgrad GEMMs): that is also the evaluation path."""
 
-    def __init__(self, model, store, batch=lstm_mod.batch_size, pull_from_owner: bool = False):
+    def __init__(self, model, store, batch=lstm_mod.batch_size, pull_from_owner: bool = False,
+                 fuse_head: bool = True):
         super().__init__(model, store, batch)
+        self.fuse_head = fuse_head and model.C <= 16
         B, dev = batch, self.dev
         T, I, H, C = model.T, model.I, model.H, model.C
         self.inputs["x"] = torch.zeros(B, T, I, device=dev)
@@ -223,7 +227,8 @@ class LstmPlan(DevicePlan):
         K.lstm_fwd(self.inputs["x"], s.wt(n("kernel")), s.vec_src(n("bias")), lstm_mod.forget_bias,
                    self.h_last, self.h_last_t if train else None, self.saved if train else None,
                    wt_ptr=wt_ptr)
-        K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits, b_static=True)
+        if not (train and self.fuse_head):
+            K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits, b_static=True)
 
     def evaluate(self) -> None:
         """Fills ``losses['loss']`` and ``correct`` for the current inputs without touching
@@ -241,20 +246,25 @@ class LstmPlan(DevicePlan):
         with torch.cuda.stream(self.side):
             K.lstm_xt(self.inputs["x"], self.saved)
         self.forward(train=True)
-        K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
-                            self.dlogits_t, s.grad(n("out_b")), self.correct)
-        self._fork()
-        with torch.cuda.stream(self.side):
-            K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
-        K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh, b_static=True)
-        K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
+        if self.fuse_head:
+            K.lstm_bwd_head(s.w(n("kernel")), self.saved, s.grad(n("bias")), self.h_last, s.w_src(n("out_w")),
+                            s.vec_src(n("out_b")), self.inputs["y"], s.grad(n("out_w")), s.grad(n("out_b")),
+                            loss=self.losses["loss"], correct=self.correct, logits=self.logits, w_ptr=w_ptr)
+        else:
+            K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
+                                self.dlogits_t, s.grad(n("out_b")), self.correct)
+            self._fork()
+            with torch.cuda.stream(self.side):
+                K.gemm(self.h_last_t, self.dlogits_t, out_f32=s.grad(n("out_w")))
+            K.gemm(self.dlogits, s.w_src(n("out_w")), out_f32=self.dh, b_static=True)
+            K.lstm_bwd(s.w(n("kernel")), self.dh, self.saved, s.grad(n("bias")), w_ptr=w_ptr)
         # reduction over all (t, b) = 3584 columns: two-way split-K; the two partial sums are added
         # atomically into the zeroed gradient buffer (two addends commute: still deterministic)
         K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")), split_k=2)
         self._join()
 
     def kernels_per_step(self) -> int:
-        return 7
+        return 4 if self.fuse_head else 8
 
 
 class ScaledLstmPlan(DevicePlan):

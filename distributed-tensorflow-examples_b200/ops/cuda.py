@@ -135,6 +135,19 @@ _lib.register_signature("psb_lstm_fwd", [c_void_p, c_void_p, c_int, c_void_p, c_
 _lib.register_signature("psb_lstm_xt", [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_lstm_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int,
                                          c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p])
+
+
+class LstmHead(ctypes.Structure):
+    """Mirror of ``psb_lstm_head_t``."""
+    _fields_ = [("h_last", c_void_p), ("ld_h", c_int), ("w_out", c_void_p), ("ld_wo", c_int),
+                ("b_out", c_void_p), ("labels", c_void_p), ("ld_l", c_int), ("C", c_int),
+                ("logits", c_void_p), ("ld_logits", c_int), ("loss", c_void_p), ("correct", c_void_p),
+                ("d_w_out", c_void_p), ("ld_dwo", c_int), ("d_b_out", c_void_p), ("scratch", c_void_p)]
+
+
+_lib.register_signature("psb_lstm_bwd_head", [c_void_p, c_int, ctypes.POINTER(LstmHead), c_void_p, c_void_p, c_int,
+                                              c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p])
+_lib.register_signature("psb_lstm_head_scratch_floats", [c_int])      # small: fits the int return
 _lib.register_signature("psb_cast_transpose", [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                                c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_mse_sigmoid_grad", [c_void_p, c_int, c_void_p, c_int, c_int, c_int,
@@ -163,6 +176,7 @@ class LstmSaved:
         self.xh_t = BMat(I + H, self.ctas * T * 16, device)
         self.dg_t = BMat(4 * H, self.ctas * T * 16, device)
         self.dbias_scratch = torch.zeros(self.ctas * 4 * H + 1, dtype=torch.float32, device=device)
+        self.head_scratch = None      # allocated by lstm_bwd_head on first use
 
     def gates_tbh(self) -> torch.Tensor:
         """Activated gates as ``[T, 4, B, H]`` (debug/tests)."""
@@ -215,6 +229,27 @@ def lstm_bwd(w: BMat, dh_last: torch.Tensor, saved: LstmSaved, dbias: torch.Tens
         saved.gates.data_ptr(), saved.c_all.data_ptr(), saved.B, saved.T, saved.I, saved.H,
         saved.dg_t.ptr, saved.dg_t.ld, dbias.data_ptr(), saved.dbias_scratch.data_ptr(),
         current_stream_ptr()), "psb_lstm_bwd")
+
+
+def lstm_bwd_head(w: BMat, saved: LstmSaved, dbias: torch.Tensor, h_last: BMat, w_out: BMat, b_out: torch.Tensor,
+                  labels: torch.Tensor, d_w_out: torch.Tensor, d_b_out: torch.Tensor,
+                  loss: Optional[torch.Tensor] = None, correct: Optional[torch.Tensor] = None,
+                  logits: Optional[torch.Tensor] = None, w_ptr: Optional[int] = None) -> None:
+    """:func:`lstm_bwd` with the classifier head fused in front of it: logits, softmax-CE, their
+    gradients (``d_w_out`` fp32 [H,C] and ``d_b_out`` [C] accumulate) and ``dh_last`` are computed
+    inside the BPTT kernel from ``h_last`` (what :func:`lstm_fwd` wrote) and ``labels`` [B,C]."""
+    C = labels.shape[1]
+    if saved.head_scratch is None:
+        n = _lib.lib().psb_lstm_head_scratch_floats(saved.B)
+        saved.head_scratch = torch.zeros(n, dtype=torch.float32, device=saved.gates.device)
+    hd = LstmHead(h_last.ptr, h_last.ld, w_out.ptr, w_out.ld, b_out.data_ptr(), labels.data_ptr(), labels.stride(0), C,
+                  logits.data_ptr() if logits is not None else None, logits.stride(0) if logits is not None else 0,
+                  loss.data_ptr() if loss is not None else None, correct.data_ptr() if correct is not None else None,
+                  d_w_out.data_ptr(), d_w_out.stride(0), d_b_out.data_ptr(), saved.head_scratch.data_ptr())
+    check(_lib.lib().psb_lstm_bwd_head(
+        w_ptr if w_ptr is not None else w.ptr, w.ld, ctypes.byref(hd), saved.gates.data_ptr(), saved.c_all.data_ptr(),
+        saved.B, saved.T, saved.I, saved.H, saved.dg_t.ptr, saved.dg_t.ld, dbias.data_ptr(),
+        saved.dbias_scratch.data_ptr(), current_stream_ptr()), "psb_lstm_bwd_head")
 
 
 # --------------------------------------------------------------------------- cast / losses

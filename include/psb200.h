@@ -119,6 +119,33 @@ int psb_lstm_bwd(const void* w, int ld_w, const float* dh_last, int ld_dh, const
                  const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
                  float* dbias, float* dbias_scratch, void* stream);
 
+/* psb_lstm_bwd with the classifier head of the LSTM model fused into its prologue: instead of
+ * reading dh_last, each CTA computes for its 16 batch rows logits = h_last W_out + b_out, the
+ * softmax cross-entropy against `labels`, dlogits, and dh_last = dlogits W_out^T on the spot, and
+ * leaves partial dW_out / db_out / loss / correct sums in `scratch` that the last CTA adds in CTA
+ * order (bit-reproducible).  d_w_out and d_b_out are accumulated (+=), loss (mean over B) and
+ * correct (count of argmax matches) are overwritten; logits is optional.  C <= 16.
+ * `scratch` holds psb_lstm_head_scratch_floats(B) floats; dbias_scratch is required (it carries
+ * the completion counter).
+ * ref: outputs[-1] W + b, softmax_cross_entropy_with_logits, accuracy and their gradients,
+ * lstm:53,92-100. */
+typedef struct {
+    const void* h_last; int ld_h;        /* bf16 [B, ld_h], written by psb_lstm_fwd */
+    const void* w_out; int ld_wo;        /* bf16 [H, ld_wo] */
+    const float* b_out;                  /* [C] */
+    const float* labels; int ld_l;       /* fp32 [B, ld_l] one-hot or soft */
+    int C;
+    float* logits; int ld_logits;        /* optional fp32 [B, ld_logits] */
+    float* loss; float* correct;         /* optional scalars */
+    float* d_w_out; int ld_dwo;          /* fp32 [H, ld_dwo] += */
+    float* d_b_out;                      /* fp32 [C] += */
+    float* scratch;
+} psb_lstm_head_t;
+size_t psb_lstm_head_scratch_floats(int B);
+int psb_lstm_bwd_head(const void* w, int ld_w, const psb_lstm_head_t* head, const void* gates,
+                      const float* c_all, int B, int T, int I, int H, void* dg_t, int ld_dgt,
+                      float* dbias, float* dbias_scratch, void* stream);
+
 /* ------------------------------------------------------------------ large-H LSTM path
  * Pointwise halves of a BasicLSTMCell step for hidden sizes whose kernel cannot be resident on
  * one SM (the scaled 2-layer H=4096 configuration): the gate GEMMs run through psb_gemm_bf16.

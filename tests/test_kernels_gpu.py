@@ -49,6 +49,47 @@ def test_lstm_fwd_bwd(B, T, I):
     assert _rel(dk, dk_ref) < 5e-2
 
 
+@pytest.mark.parametrize("B,T,C", [(128, 28, 10), (40, 6, 16), (16, 3, 3)])
+def test_lstm_bwd_fused_head(B, T, C):
+    """psb_lstm_bwd_head == head GEMM + softmax-CE + head gradients + psb_lstm_bwd (fp32 oracle), twice in
+    a row (the partial-sum scratch and its counter must reset themselves)."""
+    from psb200.ops import cuda as K_
+    from psb200.ops import reference as R
+    H, I = 128, 28
+    g = torch.Generator().manual_seed(1)
+    x = torch.rand(B, T, I, generator=g).cuda()
+    kernel = ((torch.rand(I + H, 4 * H, generator=g) * 2 - 1) * 0.2).cuda()
+    bias = (torch.randn(4 * H, generator=g) * 0.1).cuda()
+    w_out = torch.randn(H, C, generator=g).cuda()
+    b_out = torch.randn(C, generator=g).cuda()
+    labels = torch.eye(C)[torch.randint(0, C, (B,), generator=g)].cuda()
+    W, Wt, Wo = K_.BMat.from_tensor(kernel), K_.BMat.from_tensor(kernel.t().contiguous()), K_.BMat.from_tensor(w_out)
+    h_last, saved = K_.BMat(B, H), K_.LstmSaved(B, T, I, H)
+    K_.lstm_xt(x, saved)
+    K_.lstm_fwd(x, Wt, bias, 1.0, h_last, None, saved)
+    loss, correct = torch.zeros((), device="cuda"), torch.zeros((), device="cuda")
+    logits = torch.zeros(B, C, device="cuda")
+    # oracle on the kernel's own h_last (bf16) and bf16-rounded head weights
+    hq, woq = h_last.float()[:, :H], Wo.float()[:, :C]
+    z_ref = hq @ woq + b_out
+    loss_ref, dz_ref = R.softmax_xent(z_ref, labels)
+    _, sv = R.lstm_fwd(x, W.float(), bias, 1.0)
+    dk_ref, db_ref = R.lstm_bwd(dz_ref @ woq.t(), sv, W.float())
+    for _ in range(2):
+        dbias, dwo, dbo = torch.zeros(4 * H, device="cuda"), torch.zeros(H, C, device="cuda"), torch.zeros(C, device="cuda")
+        K_.lstm_bwd_head(W, saved, dbias, h_last, Wo, b_out, labels, dwo, dbo, loss=loss, correct=correct, logits=logits)
+        dk = torch.zeros(I + H, 4 * H, device="cuda")
+        K_.gemm(saved.xh_t, saved.dg_t, out_f32=dk)
+        torch.cuda.synchronize()
+        assert _rel(logits, z_ref) < 1e-4
+        assert abs(loss.item() - loss_ref.item()) < 1e-3 * max(1.0, abs(loss_ref.item()))
+        assert correct.item() == (z_ref.argmax(1) == labels.argmax(1)).sum().item()
+        assert _rel(dwo, hq.t() @ dz_ref) < 1e-3
+        assert _rel(dbo, dz_ref.sum(0)) < 1e-3
+        assert _rel(dbias, db_ref) < 5e-2
+        assert _rel(dk, dk_ref) < 5e-2
+
+
 def test_cast_transpose():
     from psb200.ops import cuda as K_
     x = torch.randn(130, 100, device="cuda")

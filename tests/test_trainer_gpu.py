@@ -33,11 +33,13 @@ def _apply(model, values, grads_by_op):
     return new
 
 
-@pytest.mark.parametrize("name", ["lstm", "encoder", "gan"])
+@pytest.mark.parametrize("name", ["lstm", "lstm_unfused_head", "encoder", "gan"])
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_one_step_matches_oracle(name, use_graph):
     from psb200.parallel.trainer import DeviceTrainer
     kw = {"device_noise": False} if name == "gan" else {}
+    if name == "lstm_unfused_head":      # head as separate kernels (the evaluation path's kernels)
+        name, kw = "lstm", {"fuse_head": False}
     tr = DeviceTrainer(name, use_graph=use_graph, seed=3, plan_kwargs=kw)
     try:
         values = tr.registry.initial_values(3)
