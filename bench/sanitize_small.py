@@ -24,7 +24,6 @@ x = torch.rand(16, 3, 28, device="cuda")
 kern = torch.randn(156, 512, device="cuda") * 0.1
 W, Wt = K.BMat.from_tensor(kern), K.BMat.from_tensor(kern.t().contiguous())
 h, ht, sv = K.BMat(16, 128), K.BMat(128, 16), K.LstmSaved(16, 3, 28, 128)
-K.lstm_xt(x, sv)
 K.lstm_fwd(x, Wt, torch.zeros(512, device="cuda"), 1.0, h, ht, sv)
 K.lstm_bwd(W, torch.randn(16, 128, device="cuda"), sv, torch.zeros(512, device="cuda"))
 torch.cuda.synchronize()

@@ -52,6 +52,7 @@ constexpr uint32_t kFwdW = 128;      // TMEM columns [128, 128 + 4*80): the cell
 constexpr int kBwdBSmem = 16 * 4 * kH * 2;      // 16384: the dG_t operand tile (16 x 512 bf16)
 constexpr int kStageRow = 144;                 // 128 data bytes + 16 pad: conflict-free 16-byte column writes
 constexpr int kFwdStage = kH * kStageRow;      // h rows x (4 steps x 16 batch) bf16, double-buffered
+constexpr int kFwdXStage = 32 * kStageRow;     // x rows (I <= 32), same slots, double-buffered
 constexpr int kBwdStage = 4 * kH * kStageRow;  // dG rows x (4 steps x 16 batch) bf16, double-buffered
 constexpr uint32_t kBwdW = 64;       // TMEM columns [64, 64 + 256): Wh (A operand); [0,64): four partial dh accumulators
 
@@ -82,6 +83,15 @@ __device__ __forceinline__ void flush_group(const uint8_t* stage, int nrows, __n
     }
 }
 
+// Same for the (at most 32) x rows of xh_t: one 16-byte chunk per pointwise thread.
+__device__ __forceinline__ void flush_x(const uint8_t* stage, int nrows, __nv_bfloat16* dst, int ld, size_t col0,
+                                        int valid_slots, uint32_t tid) {
+    const int row = static_cast<int>(tid >> 3), ch = static_cast<int>(tid & 7);
+    if (row < nrows && (ch >> 1) < valid_slots)
+        *reinterpret_cast<uint4*>(dst + static_cast<size_t>(row) * ld + col0 + ch * 8) =
+            *reinterpret_cast<const uint4*>(stage + row * kStageRow + ch * 16);
+}
+
 struct LstmFwdArgs {
     const float* x;              // [B, T, I] fp32
     const __nv_bfloat16* wt;     // [4H, ld_wt] bf16 = kernel^T (may be peer memory)
@@ -105,6 +115,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sB = smem;
     uint8_t* sStage = smem + kFwdBSmem;                  // 2 x kFwdStage
+    uint8_t* sXStage = sStage + 2 * kFwdStage;           // 2 x kFwdXStage
     __shared__ __align__(8) uint64_t xh_ready, mma_done;
     __shared__ uint32_t tmem_slot;
 
@@ -118,7 +129,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
         fence_mbar_init();
     }
     if (warp == 8) tmem_alloc<512>(&tmem_slot);
-    for (int idx = tid; idx < (kFwdBSmem + 2 * kFwdStage) / 16; idx += blockDim.x)
+    for (int idx = tid; idx < (kFwdBSmem + 2 * kFwdStage + 2 * kFwdXStage) / 16; idx += blockDim.x)
         reinterpret_cast<uint4*>(sB)[idx] = make_uint4(0, 0, 0, 0);     // operand tile and h staging (h_{-1} = 0)
     tc_fence_before_sync();
     __syncthreads();   // sB zeroed before x_0 goes in; TMEM base address published
@@ -157,6 +168,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
             const float xv = (b0 + b < a.B) ? a.x[(static_cast<size_t>(b0 + b) * a.T + 0) * a.I + i] : 0.0f;
             const __nv_bfloat16 xb = __float2bfloat16_rn(xv);
             *reinterpret_cast<__nv_bfloat16*>(sB + xh_off(b, i)) = xb;
+            if (a.gates != nullptr) *reinterpret_cast<__nv_bfloat16*>(sXStage + i * kStageRow + b * 2) = xb;   // column block 0
         }
     }
     fence_proxy_async_smem();
@@ -202,7 +214,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
         // loop-invariant addressing (no integer divisions inside the time loop)
         const uint32_t h_off = xh_off(bb, a.I + u);           // this thread's 8 batch rows of k = I+u: 16 bytes
         const float* xsrc[2];
-        uint32_t x_off[2];
+        uint32_t x_off[2], xs_off[2];
         bool x_ok[2];
 #pragma unroll
         for (int q = 0; q < 2; ++q) {
@@ -210,6 +222,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
             const int b = e / a.I, i = e % a.I;
             x_ok[q] = e < x_per_step;
             x_off[q] = x_ok[q] ? xh_off(b, i) : 0u;
+            xs_off[q] = x_ok[q] ? static_cast<uint32_t>(i * kStageRow + b * 2) : 0u;
             const bool in_batch = x_ok[q] && (b0 + b < a.B);
             xsrc[q] = in_batch ? a.x + (static_cast<size_t>(b0 + b) * a.T) * a.I + i : nullptr;
         }
@@ -249,14 +262,19 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
             if (more) {
                 // h_t -> B operand (columns I..I+H), rows bb..bb+7; x_{t+1} -> columns 0..I
                 *reinterpret_cast<uint4*>(sB + h_off) = hp;
+                // [x_{t+1}, h_t] is column block s = t+1 of xh_t: stage it (slot s&3 of buffer (s>>2)&1)
+                const int sidx = t + 1;
+                uint8_t* xs = sXStage + ((sidx >> 2) & 1) * kFwdXStage + (sidx & 3) * 32;
 #pragma unroll
-                for (int q = 0; q < 2; ++q)
-                    if (x_ok[q]) *reinterpret_cast<__nv_bfloat16*>(sB + x_off[q]) = __float2bfloat16_rn(xn[q]);
-                if (saving) {
-                    // h_t is column block s = t+1 of xh_t: stage it (slot s&3 of buffer (s>>2)&1)
-                    const int sidx = t + 1;
-                    *reinterpret_cast<uint4*>(sStage + ((sidx >> 2) & 1) * kFwdStage + u * kStageRow + (sidx & 3) * 32 + half * 16) = hp;
+                for (int q = 0; q < 2; ++q) {
+                    if (x_ok[q]) {
+                        const __nv_bfloat16 xb = __float2bfloat16_rn(xn[q]);
+                        *reinterpret_cast<__nv_bfloat16*>(sB + x_off[q]) = xb;
+                        if (saving) *reinterpret_cast<__nv_bfloat16*>(xs + xs_off[q]) = xb;
+                    }
                 }
+                if (saving)
+                    *reinterpret_cast<uint4*>(sStage + ((sidx >> 2) & 1) * kFwdStage + u * kStageRow + (sidx & 3) * 32 + half * 16) = hp;
                 tc_fence_before_sync();
                 fence_proxy_async_smem();
                 __syncwarp();
@@ -280,9 +298,12 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
                 cp[kH] = make_float4(c[4], c[5], c[6], c[7]);
                 // group (t>>2) of h columns is complete and visible (every warp staged step t-1's
                 // h before arriving on xh_ready, and this step's mma_done wait ordered after that)
-                if ((t & 3) == 3)
+                if ((t & 3) == 3) {
                     flush_group(sStage + ((t >> 2) & 1) * kFwdStage, kH, a.xh_t + static_cast<size_t>(a.I) * a.ld_xht,
                                 a.ld_xht, cta_col0 + static_cast<size_t>(t >> 2) * 64, 4, warp, lane);
+                    flush_x(sXStage + ((t >> 2) & 1) * kFwdXStage, a.I, a.xh_t, a.ld_xht,
+                            cta_col0 + static_cast<size_t>(t >> 2) * 64, 4, tid);
+                }
             }
             if (!more) {
                 const uint32_t hv[4] = {hp.x, hp.y, hp.z, hp.w};
@@ -310,16 +331,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) lstm_fwd_kernel(LstmFwdArgs a)
         const int grp = (a.T - 1) >> 2;
         flush_group(sStage + (grp & 1) * kFwdStage, kH, a.xh_t + static_cast<size_t>(a.I) * a.ld_xht, a.ld_xht,
                     static_cast<size_t>(blockIdx.x) * a.T * kNB + static_cast<size_t>(grp) * 64, a.T & 3, warp, lane);
-    }
-}
-
-// x rows of xh_t: out[i][(cta*T + t)*16 + bl] = bf16(x[cta*16 + bl][t][i])
-__global__ void lstm_xt_kernel(const float* __restrict__ x, int B, int T, int I, __nv_bfloat16* out, int ld) {
-    const int t = blockIdx.x, cta = blockIdx.y;
-    for (int e = threadIdx.x; e < I * kNB; e += blockDim.x) {
-        const int i = e / kNB, bl = e % kNB, b = cta * kNB + bl;
-        const float v = b < B ? x[(static_cast<size_t>(b) * T + t) * I + i] : 0.0f;
-        out[static_cast<size_t>(i) * ld + (static_cast<size_t>(cta) * T + t) * kNB + bl] = __float2bfloat16_rn(v);
+        flush_x(sXStage + (grp & 1) * kFwdXStage, a.I, a.xh_t, a.ld_xht,
+                static_cast<size_t>(blockIdx.x) * a.T * kNB + static_cast<size_t>(grp) * 64, a.T & 3, tid);
     }
 }
 
@@ -399,6 +412,14 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
     }
     // Wh came from the parameter arena (not written by the kernels just before us): it was loaded
     // under the tail of the head dgrad GEMM.  From here on we read what those kernels produced.
+    if (a.head.zero_ptr != nullptr) {
+        // Clear the buffer the following split-K GEMM accumulates into (nobody reads or writes it
+        // until this grid has finished), still under the previous kernel's tail.
+        uint4* z = static_cast<uint4*>(a.head.zero_ptr);
+        const size_t n16 = a.head.zero_bytes >> 4;
+        for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + tid; i < n16; i += static_cast<size_t>(gridDim.x) * blockDim.x)
+            z[i] = make_uint4(0, 0, 0, 0);
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     tc_fence_before_sync();
     __syncthreads();
@@ -661,11 +682,12 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         __syncthreads();
         if (last) {
             __threadfence();
+            const bool keep = a.head.w_out == nullptr || a.head.accumulate != 0;     // += or =
             for (int i = tid; a.dbias != nullptr && i < 4 * kH; i += blockDim.x) {
                 float s = 0.0f;
                 for (unsigned int cta = 0; cta < gridDim.x; ++cta)
                     s += *reinterpret_cast<volatile float*>(a.dbias_part + static_cast<size_t>(cta) * 4 * kH + i);
-                a.dbias[i] += s;
+                a.dbias[i] = keep ? a.dbias[i] + s : s;
             }
             if (a.head.w_out != nullptr) {
                 const psb_lstm_head_t& hd = a.head;
@@ -675,8 +697,12 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                     float s = 0.0f;
                     for (unsigned int cta = 0; cta < gridDim.x; ++cta)
                         s += *reinterpret_cast<volatile float*>(hd.scratch + static_cast<size_t>(cta) * kHeadPart + i);
-                    if (i < kH * kHeadC) { if (hd.d_w_out != nullptr) hd.d_w_out[static_cast<size_t>(i >> 4) * hd.ld_dwo + k] += s; }
-                    else if (i < kH * kHeadC + kHeadC) { if (hd.d_b_out != nullptr) hd.d_b_out[k] += s; }
+                    if (i < kH * kHeadC) {
+                        float* d = hd.d_w_out + static_cast<size_t>(i >> 4) * hd.ld_dwo + k;
+                        if (hd.d_w_out != nullptr) *d = keep ? *d + s : s;
+                    } else if (i < kH * kHeadC + kHeadC) {
+                        if (hd.d_b_out != nullptr) hd.d_b_out[k] = keep ? hd.d_b_out[k] + s : s;
+                    }
                     else if (i == kH * kHeadC + kHeadC) { if (hd.loss != nullptr) *hd.loss = s / static_cast<float>(a.B); }
                     else if (hd.correct != nullptr) *hd.correct = s;
                 }
@@ -717,7 +743,7 @@ extern "C" int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const flo
     a.h_last_t = static_cast<__nv_bfloat16*>(h_last_t); a.ld_ht = ld_ht;
     a.gates = static_cast<uint4*>(gates); a.c_all = reinterpret_cast<float4*>(c_all);
     a.xh_t = static_cast<__nv_bfloat16*>(xh_t); a.ld_xht = ld_xht;
-    const size_t smem = kFwdBSmem + 2 * kFwdStage + 1024;
+    const size_t smem = kFwdBSmem + 2 * kFwdStage + 2 * kFwdXStage + 1024;
     static bool attr = false;
     if (!attr) {
         PSB_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -741,6 +767,8 @@ static int lstm_bwd_launch(const void* w, int ld_w, const float* dh_last, int ld
             return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: h_last, w_out, b_out, labels, scratch and dbias_scratch are required");
         if (head->C < 1 || head->C > kHeadC || head->ld_wo < head->C || head->ld_h < kH)
             return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: 1 <= C <= 16, ld_wo >= C, ld_h >= H");
+        if (head->zero_ptr && ((reinterpret_cast<uintptr_t>(head->zero_ptr) | head->zero_bytes) & 15))
+            return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: zero_ptr and zero_bytes must be multiples of 16");
     }
     if (ld_w % 8 || ld_w < 4 * H) return fail(PSB_ERR_ARG, "psb_lstm_bwd: ld_w must be a multiple of 8 covering 4H");
     if (dg_t && (ld_dgt % 8 || ld_dgt < ((B + kNB - 1) / kNB) * T * kNB))
@@ -790,16 +818,4 @@ extern "C" int psb_lstm_bwd_head(const void* w, int ld_w, const psb_lstm_head_t*
     if (!head) return psb::fail(psb::PSB_ERR_ARG, "psb_lstm_bwd_head: head is required");
     return lstm_bwd_launch(w, ld_w, nullptr, 0, head, gates, c_all, B, T, I, H, dg_t, ld_dgt, dbias,
                            dbias_scratch, stream);
-}
-
-
-// The x rows of xh_t (rows 0..I-1, same column order as psb_lstm_fwd's h rows).  Separate entry
-// point so that it can run on another stream: only the weight-gradient GEMM needs it.
-extern "C" int psb_lstm_xt(const float* x, int B, int T, int I, void* xh_t, int ld_xht, void* stream) {
-    using namespace psb;
-    const int ctas = (B + kNB - 1) / kNB;
-    if (!x || !xh_t || B < 1 || T < 1 || I < 1) return fail(PSB_ERR_ARG, "psb_lstm_xt: bad argument");
-    if (ld_xht % 8 || ld_xht < ctas * T * kNB) return fail(PSB_ERR_ARG, "psb_lstm_xt: xh_t needs ceil(B/16)*T*16 columns, ld%%8==0");
-    lstm_xt_kernel<<<dim3(T, ctas), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, B, T, I, static_cast<__nv_bfloat16*>(xh_t), ld_xht);
-    return after_launch("lstm_xt");
 }

@@ -47,6 +47,13 @@ class DevicePlan:
     def _join(self) -> None:
         torch.cuda.current_stream().wait_stream(self.side)
 
+    def _zero_grads_on_side(self) -> None:
+        """Clear the gradient buffer on the side stream: the forward kernels do not touch it, so the
+        fill leaves the critical path; callers ``_join()`` before the first gradient is produced."""
+        self._fork()
+        with torch.cuda.stream(self.side):
+            self.store.zero_grads()
+
     def _name(self, key: str) -> str:
         return self.model.var[key].name
 
@@ -92,9 +99,11 @@ class EncoderPlan(DevicePlan):
 
     def forward_backward(self) -> None:
         s, n = self.store, self._name
-        s.zero_grads()
-        self.losses["loss"].zero_()
+        self._zero_grads_on_side()
+        with torch.cuda.stream(self.side):
+            self.losses["loss"].zero_()
         self.forward()
+        self._join()
         K.mse_sigmoid_grad(self.y, self.inputs["x"], self.losses["loss"], self.dz[4], self.dz_t[4],
                            s.grad(n(self.bkeys[3])))
         for l in range(3, -1, -1):
@@ -160,8 +169,9 @@ class GanPlan(DevicePlan):
 
     def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
         s, n, B = self.store, self._name, self.B
-        s.zero_grads()
+        self._zero_grads_on_side()
         self.forward()
+        self._join()
         K.gan_loss_grad(self.logit, B, self.losses_t, self.d_disc, self.d_disc_t, self.d_gen,
                         s.grad(n("b_disc_out")) if disc else None)
         if disc:
@@ -240,17 +250,17 @@ class LstmPlan(DevicePlan):
     def forward_backward(self) -> None:
         s, n = self.store, self._name
         _, w_ptr = self._kernel_ptrs()
-        s.zero_grads()
-        # the transposed inputs are only read by the last GEMM of the step: side stream
-        self._fork()
-        with torch.cuda.stream(self.side):
-            K.lstm_xt(self.inputs["x"], self.saved)
-        self.forward(train=True)
         if self.fuse_head:
+            # no separate clear of the gradient buffer: the BPTT kernel overwrites the three small
+            # gradients and zeroes the cell-kernel gradient (what the split-K GEMM below adds into)
+            self.forward(train=True)
             K.lstm_bwd_head(s.w(n("kernel")), self.saved, s.grad(n("bias")), self.h_last, s.w_src(n("out_w")),
                             s.vec_src(n("out_b")), self.inputs["y"], s.grad(n("out_w")), s.grad(n("out_b")),
-                            loss=self.losses["loss"], correct=self.correct, logits=self.logits, w_ptr=w_ptr)
+                            loss=self.losses["loss"], correct=self.correct, logits=self.logits, w_ptr=w_ptr,
+                            accumulate=False, zero=s.grad(n("kernel")))
         else:
+            s.zero_grads()
+            self.forward(train=True)
             K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
                                 self.dlogits_t, s.grad(n("out_b")), self.correct)
             self._fork()
@@ -261,10 +271,11 @@ class LstmPlan(DevicePlan):
         # reduction over all (t, b) = 3584 columns: two-way split-K; the two partial sums are added
         # atomically into the zeroed gradient buffer (two addends commute: still deterministic)
         K.gemm(self.saved.xh_t, self.saved.dg_t, out_f32=s.grad(n("kernel")), split_k=2)
-        self._join()
+        if not self.fuse_head:
+            self._join()
 
     def kernels_per_step(self) -> int:
-        return 4 if self.fuse_head else 8
+        return 3 if self.fuse_head else 7
 
 
 class ScaledLstmPlan(DevicePlan):

@@ -132,7 +132,6 @@ from ctypes import c_float, c_int, c_void_p  # noqa: E402
 _lib.register_signature("psb_lstm_fwd", [c_void_p, c_void_p, c_int, c_void_p, c_float, c_int, c_int,
                                          c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p,
                                          c_void_p, c_void_p, c_int, c_void_p])
-_lib.register_signature("psb_lstm_xt", [c_void_p, c_int, c_int, c_int, c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_lstm_bwd", [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int,
                                          c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p])
 
@@ -142,7 +141,8 @@ class LstmHead(ctypes.Structure):
     _fields_ = [("h_last", c_void_p), ("ld_h", c_int), ("w_out", c_void_p), ("ld_wo", c_int),
                 ("b_out", c_void_p), ("labels", c_void_p), ("ld_l", c_int), ("C", c_int),
                 ("logits", c_void_p), ("ld_logits", c_int), ("loss", c_void_p), ("correct", c_void_p),
-                ("d_w_out", c_void_p), ("ld_dwo", c_int), ("d_b_out", c_void_p), ("scratch", c_void_p)]
+                ("d_w_out", c_void_p), ("ld_dwo", c_int), ("d_b_out", c_void_p), ("scratch", c_void_p),
+                ("accumulate", c_int), ("zero_ptr", c_void_p), ("zero_bytes", ctypes.c_size_t)]
 
 
 _lib.register_signature("psb_lstm_bwd_head", [c_void_p, c_int, ctypes.POINTER(LstmHead), c_void_p, c_void_p, c_int,
@@ -213,13 +213,6 @@ def lstm_fwd(x: torch.Tensor, wt: BMat, bias: torch.Tensor, forget_bias: float,
         current_stream_ptr()), "psb_lstm_fwd")
 
 
-def lstm_xt(x: torch.Tensor, saved: "LstmSaved") -> None:
-    """Input rows of ``saved.xh_t`` (needed only by the weight-gradient GEMM; any stream)."""
-    B, T, I = x.shape
-    check(_lib.lib().psb_lstm_xt(x.data_ptr(), B, T, I, saved.xh_t.ptr, saved.xh_t.ld, current_stream_ptr()),
-          "psb_lstm_xt")
-
-
 def lstm_bwd(w: BMat, dh_last: torch.Tensor, saved: LstmSaved, dbias: torch.Tensor,
              w_ptr: Optional[int] = None) -> None:
     """``w`` = cell kernel natural layout bf16 [I+H, 4H]; ``dh_last`` fp32 [B,H]; fills
@@ -234,10 +227,13 @@ def lstm_bwd(w: BMat, dh_last: torch.Tensor, saved: LstmSaved, dbias: torch.Tens
 def lstm_bwd_head(w: BMat, saved: LstmSaved, dbias: torch.Tensor, h_last: BMat, w_out: BMat, b_out: torch.Tensor,
                   labels: torch.Tensor, d_w_out: torch.Tensor, d_b_out: torch.Tensor,
                   loss: Optional[torch.Tensor] = None, correct: Optional[torch.Tensor] = None,
-                  logits: Optional[torch.Tensor] = None, w_ptr: Optional[int] = None) -> None:
+                  logits: Optional[torch.Tensor] = None, w_ptr: Optional[int] = None, accumulate: bool = True,
+                  zero: Optional[torch.Tensor] = None) -> None:
     """:func:`lstm_bwd` with the classifier head fused in front of it: logits, softmax-CE, their
     gradients (``d_w_out`` fp32 [H,C] and ``d_b_out`` [C] accumulate) and ``dh_last`` are computed
-    inside the BPTT kernel from ``h_last`` (what :func:`lstm_fwd` wrote) and ``labels`` [B,C]."""
+    inside the BPTT kernel from ``h_last`` (what :func:`lstm_fwd` wrote) and ``labels`` [B,C].
+    ``accumulate=False`` overwrites the three gradients instead; ``zero`` is a tensor the kernel
+    clears in its prologue (the cell-kernel gradient the split-K wgrad GEMM then accumulates into)."""
     C = labels.shape[1]
     if saved.head_scratch is None:
         n = _lib.lib().psb_lstm_head_scratch_floats(saved.B)
@@ -245,7 +241,9 @@ def lstm_bwd_head(w: BMat, saved: LstmSaved, dbias: torch.Tensor, h_last: BMat, 
     hd = LstmHead(h_last.ptr, h_last.ld, w_out.ptr, w_out.ld, b_out.data_ptr(), labels.data_ptr(), labels.stride(0), C,
                   logits.data_ptr() if logits is not None else None, logits.stride(0) if logits is not None else 0,
                   loss.data_ptr() if loss is not None else None, correct.data_ptr() if correct is not None else None,
-                  d_w_out.data_ptr(), d_w_out.stride(0), d_b_out.data_ptr(), saved.head_scratch.data_ptr())
+                  d_w_out.data_ptr(), d_w_out.stride(0), d_b_out.data_ptr(), saved.head_scratch.data_ptr(),
+                  1 if accumulate else 0, zero.data_ptr() if zero is not None else None,
+                  zero.numel() * zero.element_size() if zero is not None else 0)
     check(_lib.lib().psb_lstm_bwd_head(
         w_ptr if w_ptr is not None else w.ptr, w.ld, ctypes.byref(hd), saved.gates.data_ptr(), saved.c_all.data_ptr(),
         saved.B, saved.T, saved.I, saved.H, saved.dg_t.ptr, saved.dg_t.ld, dbias.data_ptr(),

@@ -49,9 +49,24 @@ class DeviceTrainer:
         self._loss_keys = list(self.plan.losses.keys())
         self._host_losses = torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory()
         self._host_step = torch.zeros(1, dtype=torch.int32).pin_memory()
-        self._dev_losses = torch.zeros(len(self._loss_keys), device=self.store.device)
+        # one D2H per step for all losses: when the plan already keeps them next to each other the
+        # copy reads them in place, otherwise they are gathered first
+        self._dev_losses = self._adjacent_losses()
+        self._gather_losses = self._dev_losses is None
+        if self._gather_losses:
+            self._dev_losses = torch.zeros(len(self._loss_keys), device=self.store.device)
         self.local_step = 0
         self._launches_per_step = 0
+
+    def _adjacent_losses(self) -> Optional[torch.Tensor]:
+        ts = [self.plan.losses[k] for k in self._loss_keys]
+        base = ts[0]
+        for i, t in enumerate(ts):
+            if (t.dtype != torch.float32 or t.dim() != 0
+                    or t.untyped_storage().data_ptr() != base.untyped_storage().data_ptr()
+                    or t.storage_offset() != base.storage_offset() + i):
+                return None
+        return base.as_strided((len(ts),), (1,), base.storage_offset())
 
     # ------------------------------------------------------------------ lifecycle
     def initialize(self, values: Optional[Dict[str, torch.Tensor]] = None) -> None:
@@ -83,8 +98,9 @@ class DeviceTrainer:
         else:
             self.plan.forward_backward()
             self.store.push()
-        for i, k in enumerate(self._loss_keys):
-            self._dev_losses[i:i + 1].copy_(self.plan.losses[k].reshape(1))
+        if self._gather_losses:
+            for i, k in enumerate(self._loss_keys):
+                self._dev_losses[i:i + 1].copy_(self.plan.losses[k].reshape(1))
 
     def _warm_up(self) -> None:
         """One eager step on scratch state: sets kernel attributes, fills the TMA descriptor

@@ -104,10 +104,6 @@ int psb_lstm_fwd(const float* x, const void* wt, int ld_wt, const float* bias, f
                  int B, int T, int I, int H, void* h_last, int ld_h, void* h_last_t, int ld_ht,
                  void* gates, float* c_all, void* xh_t, int ld_xht, void* stream);
 
-/* Rows 0..I-1 of xh_t (the inputs, transposed into the column order above).  psb_lstm_fwd writes
- * only the h rows; this small kernel may run on any stream before the weight-gradient GEMM. */
-int psb_lstm_xt(const float* x, int B, int T, int I, void* xh_t, int ld_xht, void* stream);
-
 /* BPTT for psb_lstm_fwd when only the last hidden state feeds the loss.  `w` is the cell kernel
  * in its natural layout, bf16 [I+H, ld_w]; dh_last fp32 [B, ld_dh].  Writes the gate gradients
  * transposed, dg_t bf16 [4H, ld_dgt] (column t*B+b), and adds the bias gradient into dbias fp32
@@ -140,6 +136,9 @@ typedef struct {
     float* d_w_out; int ld_dwo;          /* fp32 [H, ld_dwo] += */
     float* d_b_out;                      /* fp32 [C] += */
     float* scratch;
+    int accumulate;                      /* 0: d_w_out, d_b_out and dbias are overwritten instead of += */
+    void* zero_ptr; size_t zero_bytes;   /* optional buffer cleared in the prologue (16-byte multiples),
+                                            e.g. the gradient a following split-K GEMM accumulates into */
 } psb_lstm_head_t;
 size_t psb_lstm_head_scratch_floats(int B);
 int psb_lstm_bwd_head(const void* w, int ld_w, const psb_lstm_head_t* head, const void* gates,

@@ -25,7 +25,6 @@ def test_lstm_fwd_bwd(B, T, I):
     Wt = K_.BMat.from_tensor(kernel.t().contiguous())   # [4H, I+H]
     h_last, h_last_t = K_.BMat(B, H), K_.BMat(H, B)
     saved = K_.LstmSaved(B, T, I, H)
-    K_.lstm_xt(x, saved)
     K_.lstm_fwd(x, Wt, bias, 1.0, h_last, h_last_t, saved)
     torch.cuda.synchronize()
 
@@ -65,7 +64,6 @@ def test_lstm_bwd_fused_head(B, T, C):
     labels = torch.eye(C)[torch.randint(0, C, (B,), generator=g)].cuda()
     W, Wt, Wo = K_.BMat.from_tensor(kernel), K_.BMat.from_tensor(kernel.t().contiguous()), K_.BMat.from_tensor(w_out)
     h_last, saved = K_.BMat(B, H), K_.LstmSaved(B, T, I, H)
-    K_.lstm_xt(x, saved)
     K_.lstm_fwd(x, Wt, bias, 1.0, h_last, None, saved)
     loss, correct = torch.zeros((), device="cuda"), torch.zeros((), device="cuda")
     logits = torch.zeros(B, C, device="cuda")
@@ -75,11 +73,17 @@ def test_lstm_bwd_fused_head(B, T, C):
     loss_ref, dz_ref = R.softmax_xent(z_ref, labels)
     _, sv = R.lstm_fwd(x, W.float(), bias, 1.0)
     dk_ref, db_ref = R.lstm_bwd(dz_ref @ woq.t(), sv, W.float())
-    for _ in range(2):
-        dbias, dwo, dbo = torch.zeros(4 * H, device="cuda"), torch.zeros(H, C, device="cuda"), torch.zeros(C, device="cuda")
-        K_.lstm_bwd_head(W, saved, dbias, h_last, Wo, b_out, labels, dwo, dbo, loss=loss, correct=correct, logits=logits)
-        dk = torch.zeros(I + H, 4 * H, device="cuda")
-        K_.gemm(saved.xh_t, saved.dg_t, out_f32=dk)
+    for accumulate in (True, False):
+        if accumulate:
+            dbias, dwo, dbo = torch.zeros(4 * H, device="cuda"), torch.zeros(H, C, device="cuda"), torch.zeros(C, device="cuda")
+            dk = torch.zeros(I + H, 4 * H, device="cuda")
+            K_.lstm_bwd_head(W, saved, dbias, h_last, Wo, b_out, labels, dwo, dbo, loss=loss, correct=correct, logits=logits)
+        else:       # overwrite mode: stale contents must not survive, and the kernel clears dk itself
+            dbias, dwo, dbo = torch.full((4 * H,), 7.0, device="cuda"), torch.full((H, C), 7.0, device="cuda"), torch.full((C,), 7.0, device="cuda")
+            dk = torch.full((I + H, 4 * H), 7.0, device="cuda")
+            K_.lstm_bwd_head(W, saved, dbias, h_last, Wo, b_out, labels, dwo, dbo, loss=loss, correct=correct,
+                             logits=logits, accumulate=False, zero=dk)
+        K_.gemm(saved.xh_t, saved.dg_t, out_f32=dk, split_k=2)
         torch.cuda.synchronize()
         assert _rel(logits, z_ref) < 1e-4
         assert abs(loss.item() - loss_ref.item()) < 1e-3 * max(1.0, abs(loss_ref.item()))
