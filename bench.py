@@ -13,8 +13,9 @@ For N > 1 launch with ``python -m torch.distributed.run --nproc-per-node N ... b
 Timing: every step is bracketed by its own pair of CUDA events on the launching stream;
 between steps a 256 MiB buffer is overwritten to flush the 126 MB L2 (outside the event
 pairs); the reported time is the sum of the K step durations, max over ranks.  The e2e arm
-drives the public API (``DeviceTrainer.step``): pinned-host batch -> H2D -> step -> D2H of
-loss and global_step, every step.
+drives the public API: pinned-host batch -> H2D -> step -> D2H of loss and global_step, every
+step, through ``DeviceTrainer.step_async`` (pipelined; headline) and ``DeviceTrainer.step``
+(host blocks on every step; reported as ``blocking_api_*``).
 """
 from __future__ import annotations
 
@@ -171,6 +172,13 @@ def run_psb200(args):
     def e2e_step(i):
         tr.step(batches[i % len(batches)])
 
+    def e2e_pipelined(i):
+        # same work per step (H2D from pinned memory, step, D2H of loss + global_step); the host
+        # does not wait for step i before submitting step i+1, results come back one call later
+        tr.step_async(batches[i % len(batches)])
+        if i == args.steps - 1:
+            tr.drain()
+
     for i in range(args.warmup):
         dev_step(i)
     torch.cuda.synchronize()
@@ -186,7 +194,11 @@ def run_psb200(args):
         launches = tr.launches_per_step() * args.steps      # graph replays do not pass through the launcher
     for i in range(args.warmup):
         e2e_step(i)
-    ms_e2e = timed_e2e_steps(e2e_step, args.steps, world)
+    ms_e2e_sync = timed_e2e_steps(e2e_step, args.steps, world)
+    for i in range(args.warmup):
+        tr.step_async(batches[i % len(batches)])
+    tr.drain()
+    ms_e2e = timed_e2e_steps(e2e_pipelined, args.steps, world)
     clocks = sampler.stop() if rank == 0 else None
     last = tr.step(batches[0])
     gstep = last["global_step"]
@@ -212,7 +224,11 @@ def run_psb200(args):
             "clocks": clocks,
             "e2e": {"value": round(e2e, 1), "unit": "examples/s", "ms_per_step": round(ms_e2e / args.steps, 4),
                     "h2d_bytes_per_step": tr.h2d_bytes_per_step(batches[0]),
-                    "d2h_bytes_per_step": tr.d2h_bytes_per_step()},
+                    "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
+                    "api": "DeviceTrainer.step_async: every step copies its batch from pinned host memory and "
+                           "reads loss+global_step back; submission of step i+1 overlaps step i",
+                    "blocking_api_value": round(total / (ms_e2e_sync / 1e3), 1),
+                    "blocking_api_ms_per_step": round(ms_e2e_sync / args.steps, 4)},
             "gpu_launches": int(launches),
             "push_pull_us_per_step": {k: round(v, 2) for k, v in push_prof.items() if k != "calls"},
             "final": {"global_step": gstep, "losses": {k: v for k, v in last.items() if k != "global_step"}},

@@ -5,6 +5,7 @@
     tr = DeviceTrainer("lstm", rank, world, group, mode="sync")
     tr.initialize()                       # chief init_op (or restore) + first parameter pull
     out = tr.step({"x": x_pinned, "y": y_pinned})     # H2D, graph replay, loss D2H
+    prev = tr.step_async(next_batch)      # same, pipelined: returns the PREVIOUS step's result
 
 One step = the model's device plan (forward, losses, backward: hand-written sm_100a
 kernels) followed by the fused gradient push (reduce-scatter + optimizer + all-gather in
@@ -57,6 +58,7 @@ class DeviceTrainer:
             self._dev_losses = torch.zeros(len(self._loss_keys), device=self.store.device)
         self.local_step = 0
         self._launches_per_step = 0
+        self._pipe = None           # step_async state, built on first use
 
     def _adjacent_losses(self) -> Optional[torch.Tensor]:
         ts = [self.plan.losses[k] for k in self._loss_keys]
@@ -145,6 +147,65 @@ class DeviceTrainer:
         out = {k: float(self._host_losses[i]) for i, k in enumerate(self._loss_keys)}
         out["global_step"] = int(self._host_step[0])
         return out
+
+    # ---- pipelined stepping: input prefetch on a copy stream, results read one step late
+    def _pipe_state(self):
+        if self._pipe is None:
+            dev = self.store.device
+            self._pipe = {
+                "seq": 0, "stream": torch.cuda.Stream(device=dev),
+                "stage": [{k: torch.empty_like(v) for k, v in self.plan.inputs.items()} for _ in range(2)],
+                "losses": [torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory() for _ in range(2)],
+                "gstep": [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(2)],
+                "h2d": [torch.cuda.Event() for _ in range(2)], "consumed": [torch.cuda.Event() for _ in range(2)],
+                "done": [torch.cuda.Event() for _ in range(2)], "pending": [False, False],
+            }
+        return self._pipe
+
+    def _pipe_result(self, k: int) -> Dict[str, float]:
+        p = self._pipe
+        p["done"][k].synchronize()
+        p["pending"][k] = False
+        out = {key: float(p["losses"][k][i]) for i, key in enumerate(self._loss_keys)}
+        out["global_step"] = int(p["gstep"][k][0])
+        return out
+
+    def step_async(self, batch: Dict[str, torch.Tensor]) -> Optional[Dict[str, float]]:
+        """Pipelined :meth:`step`: enqueue this batch's H2D (copy stream, into one of two staging
+        sets), the step and the D2H of its results WITHOUT waiting for them, then return the result
+        of the previously submitted step (``None`` on the first call; :meth:`drain` returns the
+        last).  The host never idles the GPU between steps: the next batch's copy overlaps the
+        running step.  ``batch`` must be pinned and stay unmodified until its result is returned."""
+        p = self._pipe_state()
+        k = p["seq"] & 1
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(p["stream"]):
+            if p["seq"] >= 2:
+                p["stream"].wait_event(p["consumed"][k])          # staging set k was read by step seq-2
+            for name, v in batch.items():
+                if name in self.plan.inputs:
+                    p["stage"][k][name].copy_(v.reshape(self.plan.inputs[name].shape), non_blocking=True)
+            p["h2d"][k].record(p["stream"])
+        main.wait_event(p["h2d"][k])
+        for name, t in p["stage"][k].items():
+            if name in batch:
+                self.plan.inputs[name].copy_(t, non_blocking=True)
+        p["consumed"][k].record(main)
+        self.step_device()
+        p["losses"][k].copy_(self._dev_losses, non_blocking=True)
+        gs_rank = self.store.gs_owner if self.mode == "async" else self.rank
+        p["gstep"][k].copy_(self.store.heap.tensor(self.store._gs_off, (1,), torch.int32, gs_rank), non_blocking=True)
+        p["done"][k].record(main)
+        p["pending"][k] = True
+        p["seq"] += 1
+        return self._pipe_result(1 - k) if p["pending"][1 - k] else None
+
+    def drain(self) -> Optional[Dict[str, float]]:
+        """Wait for the last :meth:`step_async` submission and return its result."""
+        if self._pipe is None:
+            return None
+        k = (self._pipe["seq"] - 1) & 1
+        return self._pipe_result(k) if self._pipe["pending"][k] else None
 
     def trace_step(self) -> Dict[str, float]:
         """One EAGER (un-graphed) step with CUDA-event timing per phase: forward+backward

@@ -110,6 +110,33 @@ def test_lstm_trains_and_evaluates():
         tr.close()
 
 
+def test_step_async_matches_blocking_steps():
+    """The pipelined API produces exactly the blocking API's sequence of results, one call late."""
+    from psb200.parallel.trainer import DeviceTrainer
+    batches = [{k: v.pin_memory() for k, v in _batch("lstm", 128, 10 + i).items()} for i in range(5)]
+    want, got = [], []
+    tr = DeviceTrainer("lstm", seed=2)
+    try:
+        tr.initialize()
+        want = [tr.step(b) for b in batches]
+    finally:
+        tr.close()
+    tr = DeviceTrainer("lstm", seed=2)
+    try:
+        tr.initialize()
+        assert tr.drain() is None
+        for i, b in enumerate(batches):
+            r = tr.step_async(b)
+            assert (r is None) == (i == 0)
+            if r is not None:
+                got.append(r)
+        got.append(tr.drain())
+        assert tr.drain() is None
+    finally:
+        tr.close()
+    assert got == want and [g["global_step"] for g in got] == [1, 2, 3, 4, 5]
+
+
 def test_gan_device_noise_changes_every_replay():
     from psb200.parallel.trainer import DeviceTrainer
     tr = DeviceTrainer("gan", seed=2)
