@@ -54,6 +54,7 @@ def _dist_setup(n_gpus: int):
     group = None
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout to the one JSON line
         dist.init_process_group(backend="nccl", device_id=torch.device("cuda", local))
         group = dist.new_group(backend="gloo")
     return rank, world, local, group

@@ -410,6 +410,23 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
         }
         tmem_st_wait();
     }
+    // Head operands that do not depend on the forward kernel (parameters, labels) are fetched here,
+    // under the previous kernel's tail: W_out -> shared memory, this thread's label and bias.
+    float head_y = 0.0f, head_b = 0.0f;
+    if (warp < 8 && a.head.w_out != nullptr) {
+        const psb_lstm_head_t& hd = a.head;
+        float* sW = reinterpret_cast<float*>(sStage) + kNB * 129;
+        const __nv_bfloat16* wo = static_cast<const __nv_bfloat16*>(hd.w_out);
+        for (int e = static_cast<int>(tid); e < kH * kHeadC; e += kPW) {
+            const int j = e >> 4, k = e & 15;
+            sW[j * 17 + k] = (k < hd.C) ? __bfloat162float(wo[static_cast<size_t>(j) * hd.ld_wo + k]) : 0.0f;
+        }
+        const int b = static_cast<int>(tid >> 4), k = static_cast<int>(tid & 15);
+        if (k < hd.C) {
+            head_b = hd.b_out[k];
+            if (b0 + b < a.B) head_y = hd.labels[static_cast<size_t>(b0 + b) * hd.ld_l + k];
+        }
+    }
     // Wh came from the parameter arena (not written by the kernels just before us): it was loaded
     // under the tail of the head dgrad GEMM.  From here on we read what those kernels produced.
     if (a.head.zero_ptr != nullptr) {
@@ -472,14 +489,16 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
             float* sdl = sW + kH * 17;                           // [16][17]  dlogits
             float* sred = sdl + kNB * 17;                        // [16][2]   loss, correct per row
             const __nv_bfloat16* hl = static_cast<const __nv_bfloat16*>(hd.h_last);
-            const __nv_bfloat16* wo = static_cast<const __nv_bfloat16*>(hd.w_out);
-            for (int e = static_cast<int>(tid); e < kNB * kH; e += kPW) {
-                const int b = e >> 7, j = e & 127;
-                sh[b * 129 + j] = (b0 + b < a.B) ? __bfloat162float(hl[static_cast<size_t>(b0 + b) * hd.ld_h + j]) : 0.0f;
-            }
-            for (int e = static_cast<int>(tid); e < kH * kHeadC; e += kPW) {
-                const int j = e >> 4, k = e & 15;
-                sW[j * 17 + k] = (k < C) ? __bfloat162float(wo[static_cast<size_t>(j) * hd.ld_wo + k]) : 0.0f;
+            {   // h_T rows of this CTA: one 16-byte load (8 units) per thread
+                const int b = static_cast<int>(tid >> 4), j0 = static_cast<int>(tid & 15) * 8;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (b0 + b < a.B) v = *reinterpret_cast<const uint4*>(hl + static_cast<size_t>(b0 + b) * hd.ld_h + j0);
+                const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    sh[b * 129 + j0 + 2 * q] = bf16_lo(w4[q]);
+                    sh[b * 129 + j0 + 2 * q + 1] = bf16_hi(w4[q]);
+                }
             }
             asm volatile("bar.sync 1, 256;" ::: "memory");
             {
@@ -488,8 +507,8 @@ __global__ void __launch_bounds__(kLstmThreads, 1) lstm_bwd_kernel(LstmBwdArgs a
                 float z = 0.0f;
 #pragma unroll 8
                 for (int j = 0; j < kH; ++j) z = fmaf(sh[b * 129 + j], sW[j * 17 + k], z);
-                if (in_c) z += hd.b_out[k];
-                const float y = valid ? hd.labels[static_cast<size_t>(b0 + b) * hd.ld_l + k] : 0.0f;
+                z += head_b;
+                const float y = head_y;
                 const float zz = in_c ? z : -INFINITY;
                 const float mx = grp16_max(zz);
                 const int am = grp16_min((in_c && zz == mx) ? k : 99);      // first maximum, like the loss kernel
@@ -767,6 +786,8 @@ static int lstm_bwd_launch(const void* w, int ld_w, const float* dh_last, int ld
             return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: h_last, w_out, b_out, labels, scratch and dbias_scratch are required");
         if (head->C < 1 || head->C > kHeadC || head->ld_wo < head->C || head->ld_h < kH)
             return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: 1 <= C <= 16, ld_wo >= C, ld_h >= H");
+        if ((head->ld_h % 8) || (reinterpret_cast<uintptr_t>(head->h_last) & 15))
+            return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: h_last must be 16-byte aligned with ld_h%%8==0");
         if (head->zero_ptr && ((reinterpret_cast<uintptr_t>(head->zero_ptr) | head->zero_bytes) & 15))
             return fail(PSB_ERR_ARG, "psb_lstm_bwd_head: zero_ptr and zero_bytes must be multiples of 16");
     }
