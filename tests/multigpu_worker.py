@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--mode", default="sync")
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--pull_from_owner", type=int, default=0)
+    ap.add_argument("--stress", type=int, default=0)
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -55,6 +56,42 @@ def main():
         torch.cuda.synchronize()
         dist.barrier(group=group)
         return tr, values, res
+
+    if a.stress:
+        # T4: signal-pad protocol under randomised host delays.  Run A steps in lock-step through the
+        # blocking API; run B lets every rank stall for a random time before each submission and
+        # mixes the pipelined API in.  The device-side step tokens must make both runs bit-identical.
+        import random
+        import time
+        batches = [{k: v.pin_memory() for k, v in batch_for(a.model, 128 if a.model != "encoder" else 256, 400 + 7 * i + rank).items()}
+                   for i in range(4)]
+        states = []
+        for jitter in (False, True):
+            tr, _, _ = run_once()
+            rnd = random.Random(1234 + rank)
+            for i in range(a.stress):
+                if jitter:
+                    time.sleep(rnd.random() * 0.003 if rnd.random() < 0.5 else 0.0)
+                    if rnd.random() < 0.5:
+                        tr.step_async(batches[i % 4])
+                    else:
+                        tr.drain()
+                        tr.step(batches[i % 4])
+                else:
+                    tr.step(batches[i % 4])
+            tr.drain()
+            torch.cuda.synchronize()
+            dist.barrier(group=group)
+            assert tr.global_step() == (a.stress + 1) * tr.model.steps_per_run(), tr.global_step()
+            states.append(tr.variables())
+            tr.close()
+        for k in states[0]:
+            assert torch.equal(states[0][k], states[1][k]), (rank, k, "host jitter changed the result")
+        dist.barrier()
+        if rank == 0:
+            print("MULTIGPU_OK", a.model, "stress", world)
+        dist.destroy_process_group()
+        return
 
     tr, values, res = run_once()
     model = tr.model

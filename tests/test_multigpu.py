@@ -43,6 +43,13 @@ def test_pull_fused_into_consumer_kernels(model):
     _run(2, "--model", model, "--mode", "sync", "--pull_from_owner", "1")
 
 
+@pytest.mark.parametrize("model", ["lstm", "gan"])
+def test_signal_protocol_under_host_jitter(model):
+    """T4 stress: random per-rank host stalls and a mix of blocking / pipelined submissions must not
+    change a single bit of the sync-mode result (device-side step tokens order everything)."""
+    _run(2, "--model", model, "--mode", "sync", "--stress", "60")
+
+
 def test_nvl_entrypoints_through_the_reference_cli(tmp_path):
     """examples/distributed_lstm.py --backend=nvl: 1 ps (done-queue only) + 2 GPU workers, sync."""
     from psb200.launch import launch
