@@ -139,3 +139,46 @@ def test_corruption_is_detected(tmp_path):
         tf_bundle.list_variables(prefix)
     open(prefix + ".index", "wb").write(b"{}")
     assert not tf_bundle.is_tf_bundle(prefix)
+
+
+def test_random_bundles_round_trip():
+    """Property: any set of distinct names / small tensors survives write -> read bit-exactly."""
+    from hypothesis import given, settings, strategies as st
+    import tempfile
+
+    names = st.text(alphabet="abcXYZ_/0123456789", min_size=1, max_size=24)
+    shapes = st.lists(st.integers(0, 5), min_size=0, max_size=3)
+    dtypes = st.sampled_from([torch.float32, torch.int32, torch.float64, torch.int64, torch.float16, torch.bfloat16])
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.dictionaries(names, st.tuples(shapes, dtypes, st.integers(0, 2 ** 31 - 1)), min_size=1, max_size=12))
+    def check(spec):
+        vals = {}
+        for name, (shape, dt, seed) in spec.items():
+            g = torch.Generator().manual_seed(seed)
+            t = torch.randint(-1000, 1000, shape, generator=g)
+            vals[name] = t.to(dt) if not dt.is_floating_point else (t.float() / 7).to(dt)
+        with tempfile.TemporaryDirectory() as d:
+            prefix = os.path.join(d, "m")
+            tf_bundle.write_bundle(prefix, vals)
+            back = tf_bundle.read_bundle(prefix)
+            assert list(back) == sorted(vals)
+            for k, v in vals.items():
+                assert back[k].dtype == v.dtype and list(back[k].shape) == list(v.shape)
+                assert back[k].reshape(-1).contiguous().numpy().tobytes() == v.reshape(-1).contiguous().numpy().tobytes() \
+                    if v.dtype != torch.bfloat16 else torch.equal(back[k].view(torch.int16), v.view(torch.int16)), k
+
+    check()
+
+
+def test_inspect_checkpoint_tool(tmp_path, capsys):
+    from psb200.tools import inspect_checkpoint as ic
+    d = str(tmp_path)
+    Saver(bundle_format="tf").save({"Variable": torch.ones(2, 3), "Variable_2": torch.tensor(5, dtype=torch.int32)}, d, 5)
+    assert ic.main(["--file_name", d]) == 0
+    out = capsys.readouterr().out
+    assert "model.ckpt-5 (tf bundle, 2 variables)" in out and "Variable (DT_FLOAT) [2, 3]" in out and "Variable_2 (DT_INT32) []" in out
+    assert ic.main(["--file_name", os.path.join(d, "model.ckpt-5"), "--tensor_name", "Variable_2"]) == 0
+    assert capsys.readouterr().out.strip().endswith("5")
+    assert ic.main(["--file_name", d, "--tensor_name", "nope"]) == 1
+    assert ic.main(["--file_name", os.path.join(d, "missing")]) == 1
