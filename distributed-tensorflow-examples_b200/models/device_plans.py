@@ -284,7 +284,7 @@ class ScaledLstmPlan(DevicePlan):
     it and batches both weight gradients and the gradient to the layer below into large GEMMs.
     Input ``x`` is time-major fp32 ``[T, B, I]``."""
 
-    def __init__(self, model, store, batch=None):
+    def __init__(self, model, store, batch=None, fuse_fwd: bool = True):
         super().__init__(model, store, batch or model.batch_size)
         B, dev = self.B, self.dev
         T, I, H, L, C = model.T, model.I, model.H, model.L, model.C
@@ -311,7 +311,7 @@ class ScaledLstmPlan(DevicePlan):
         self.bn_fwd = 128 if big else 0
         self.bn_bwd = 64 if big else 0
         # forward timestep = ONE kernel (recurrent GEMM with the cell pointwise in its epilogue)
-        self.fuse_fwd = (H % 32 == 0) and int(__import__('os').environ.get('PSB_SCALED_FUSE', '1')) == 1
+        self.fuse_fwd = fuse_fwd and H % 32 == 0
         self.dh_rec = torch.zeros(self.split_k, B, H, device=dev)
         self.dc = torch.zeros(B, H, device=dev)
         self.dY = torch.zeros(TB, H, device=dev) if L > 1 else None  # gradient arriving from the layer above

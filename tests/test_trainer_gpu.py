@@ -174,12 +174,14 @@ def test_nvl_entrypoint_single_gpu_async_gan(tmp_path):
     assert rc == 0 and "Global step 32 Local step 0" in logs["worker:0"] and "Global step 50" in logs["worker:0"], logs
 
 
-def test_scaled_stacked_lstm_matches_oracle():
-    """2-layer large-H path (per-timestep GEMM + pointwise cell kernels, batched wgrad GEMMs) at
-    toy dimensions vs the stacked-LSTM oracle."""
+@pytest.mark.parametrize("fuse_fwd", [True, False])
+def test_scaled_stacked_lstm_matches_oracle(fuse_fwd):
+    """2-layer large-H path at toy dimensions vs the stacked-LSTM oracle: forward timestep as one fused
+    GEMM+cell kernel, or as a GEMM followed by the pointwise cell kernel; batched wgrad GEMMs."""
     from psb200.parallel.trainer import DeviceTrainer
     dims = dict(num_input=64, timesteps=6, num_hidden=128, num_layers=2, num_classes=10, lr=0.5)
-    tr = DeviceTrainer("scaled_lstm", use_graph=True, seed=4, batch=64, model_kwargs=dims)
+    tr = DeviceTrainer("scaled_lstm", use_graph=True, seed=4, batch=64, model_kwargs=dims,
+                       plan_kwargs={"fuse_fwd": fuse_fwd})
     try:
         values = tr.registry.initial_values(4)
         for s in tr.registry.trainable():
