@@ -136,3 +136,44 @@ def test_tf_bundle_checkpoints_resume(tmp_path):
     assert rc == 0, logs
     steps = _global_steps(logs["worker:0"]) + _global_steps(logs["worker:1"])
     assert min(steps) > saved - 1 and max(steps) >= saved + 4
+
+
+def test_killed_worker_rejoins_and_cluster_finishes(tmp_path):
+    """Fault injection: a non-chief worker is SIGKILLed mid-run and started again.  Async
+    workers never wait for each other (device filters), so the chief keeps training; the restarted
+    worker finds the variables initialised, continues from the shared global_step and sends the done
+    token its first incarnation never sent, which lets the ps exit."""
+    ports = _ports(3)
+    ps = ["127.0.0.1:%d" % ports[0]]
+    workers = ["127.0.0.1:%d" % p for p in ports[1:]]
+    model_dir = str(tmp_path / "ckpt")
+    extra = ["--num_steps=400", "--save_model_secs=0"]
+    p_ps = _launch("encoder", "ps", 0, ps, workers, model_dir, extra)
+    p_w0 = _launch("encoder", "worker", 0, ps, workers, model_dir, extra)
+    p_w1 = _launch("encoder", "worker", 1, ps, workers, model_dir, extra)
+    # let worker 1 make some progress, then kill it without any clean-up
+    seen = ""
+    deadline = time.time() + 120
+    while "Local step 3 " not in seen and time.time() < deadline:
+        line = p_w1.stdout.readline()
+        if not line:
+            break
+        seen += line
+    assert "Local step 3 " in seen, seen
+    p_w1.kill()
+    p_w1.wait()
+    first_steps = _global_steps(seen)
+    p_w1b = _launch("encoder", "worker", 1, ps, workers, model_dir, extra)
+    outs = {}
+    for name, p in (("w0", p_w0), ("w1b", p_w1b), ("ps", p_ps)):
+        try:
+            outs[name], _ = p.communicate(timeout=170)
+        except subprocess.TimeoutExpired:
+            for q in (p_ps, p_w0, p_w1b):
+                q.kill()
+            raise AssertionError("cluster did not finish after the restart: " + name)
+        assert p.returncode == 0, outs[name][-2000:]
+    again = _global_steps(outs["w1b"])
+    assert again and min(again) > max(first_steps)            # continued from the shared counter, no re-init
+    assert max(_global_steps(outs["w0"]) + again) >= 400
+    assert "ps 0 received done 1" in outs["ps"] and "ps 0: quitting" in outs["ps"]
