@@ -48,7 +48,7 @@ class Flags:
     save_model_secs: int = 60          # Supervisor checkpoint period
     reinit_on_join: bool = False       # reproduce `sess.run(init)` on every worker (encoder:160, gan:181)
     gan_update: str = "simultaneous"   # "simultaneous" (gan:193) | "alternating"
-    dtype: str = "fp32"                # compute dtype of the worker math: fp32 | bf16
+    dtype: str = "fp32"                # cpu backend: weight precision seen by the worker math, fp32 | bf16 (nvl: always bf16 operands, fp32 accumulate)
     seed: int = 0
     log_every: int = 1                 # print the per-step line every n local steps
     ps_wait_timeout: float = 0.0       # 0 -> ps waits forever for done tokens (reference)
@@ -102,6 +102,8 @@ def parse_flags(argv: Optional[Sequence[str]] = None, prog: Optional[str] = None
     fl.extra = list(extra)
     if fl.backend not in ("cpu", "nvl"):
         raise SystemExit("--backend must be 'cpu' or 'nvl'")
+    if fl.dtype not in ("fp32", "bf16"):
+        raise SystemExit("--dtype must be 'fp32' or 'bf16'")
     if fl.checkpoint_format not in ("psb200", "tf"):
         raise SystemExit("--checkpoint_format must be 'psb200' or 'tf'")
     if fl.gan_update not in ("simultaneous", "alternating"):

@@ -55,10 +55,20 @@ def _make_batch(model_name: str, mnist, batch_size: int, rng: np.random.RandomSt
     return {"x": torch.from_numpy(bx.reshape(batch_size, 28, 28)), "y": torch.from_numpy(by)}
 
 
+def compute_params(params: Dict[str, torch.Tensor], dtype: str) -> Dict[str, torch.Tensor]:
+    """What the worker math sees of the pulled variables.  ``--dtype=bf16`` rounds every weight
+    matrix to bf16 (the master copy on the ps stays fp32), which is the operand precision of the
+    sm_100a kernels: the CPU transport then reproduces the NVLink backend's numerics."""
+    if dtype != "bf16":
+        return params
+    return {k: (v.to(torch.bfloat16).float() if v.dim() == 2 else v) for k, v in params.items()}
+
+
 def _train_call_cpu(model, store: TcpStore, flags: Flags, batch, local_sync_step: int, sv: Supervisor):
     """One ``sess.run([train ops..., losses..., global_step], feed_dict)`` on the tcp transport."""
+    pull = lambda: compute_params(store.pull(), flags.dtype)      # noqa: E731
     if flags.sync:
-        params = store.pull()
+        params = pull()
         out = model.step_reference(params, batch)
         step = store.push_sync(out.grads, local_sync_step, sv.should_stop)
         return out.losses, step
@@ -66,12 +76,12 @@ def _train_call_cpu(model, store: TcpStore, flags: Flags, batch, local_sync_step
         losses = {}
         step = 0
         for op_name in ("train_disc", "train_gen"):
-            out = model.step_reference(store.pull(), batch)
+            out = model.step_reference(pull(), batch)
             op = [o for o in model.train_ops if o.name == op_name][0]
             step = store.push_async(op, out.grads[op.name])
             losses[op.loss] = out.losses[op.loss]
         return losses, step
-    out = model.step_reference(store.pull(), batch)
+    out = model.step_reference(pull(), batch)
     step = 0
     for op in model.train_ops:
         step = store.push_async(op, out.grads[op.name])

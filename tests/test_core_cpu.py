@@ -174,3 +174,16 @@ def test_ps_runtime_accumulator_mean_and_stale_drop(ps):
     c.acc_set_step("Variable", 1)
     assert c.acc_apply("Variable", torch.ones(4), 0) is False     # stale: dropped
     assert c.stats()["stale_dropped"] == 1
+
+
+def test_dtype_flag_rounds_weight_matrices_only():
+    from psb200.flags import parse_flags
+    from psb200.runner import compute_params
+    p = {"w": torch.tensor([[1.00390625, 2.0]]), "b": torch.tensor([1.00390625]), "step": torch.tensor(3, dtype=torch.int32)}
+    assert compute_params(p, "fp32") is p
+    q = compute_params(p, "bf16")
+    assert q["w"][0, 0].item() == 1.0 and q["w"].dtype == torch.float32        # 1 + 2^-8 is not a bf16 value
+    assert q["b"][0].item() == 1.00390625 and q["step"].dtype == torch.int32
+    assert parse_flags(["--dtype=bf16"]).dtype == "bf16"
+    with pytest.raises(SystemExit):
+        parse_flags(["--dtype=fp8"])
