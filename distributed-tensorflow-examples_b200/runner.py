@@ -150,6 +150,12 @@ def run_worker_nvl(model_name: str, flags: Flags, cluster: ClusterSpec, server: 
     from .parallel.trainer import DeviceTrainer
     world = cluster.num_tasks("worker")
     rank = flags.task_index
+    if flags.sync and flags.replicas_to_aggregate not in (0, world):
+        raise SystemExit("--backend=nvl aggregates all %d replicas per step; --replicas_to_aggregate=%d "
+                         "(backup workers) needs --backend=cpu" % (world, flags.replicas_to_aggregate))
+    if flags.reinit_on_join:
+        raise SystemExit("--reinit_on_join reproduces a tcp-transport race (encoder:160); it has no meaning on "
+                         "--backend=nvl, where all ranks initialise collectively")
     local = int(os.environ.get("LOCAL_RANK", rank % max(1, torch.cuda.device_count())))
     torch.cuda.set_device(local)
     group = None
