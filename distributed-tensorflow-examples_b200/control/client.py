@@ -70,6 +70,11 @@ def _np_dtype(dtype: torch.dtype):
     return {torch.float32: np.float32, torch.int32: np.int32}[dtype]
 
 
+def _buffer(t: torch.Tensor) -> memoryview:
+    """The tensor's bytes as a flat buffer (no copy for contiguous CPU tensors)."""
+    return memoryview(t.detach().contiguous().reshape(-1).numpy()).cast("B")
+
+
 class PsClient:
     def __init__(self, hostport: str, connect_timeout: float = 60.0):
         self.hostport = hostport
@@ -89,27 +94,41 @@ class PsClient:
         self.sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
 
     # ---- transport ---------------------------------------------------------------
-    def _call(self, op: int, name: str = "", payload: bytes = b"", what: str = "") -> bytes:
+    def _call(self, op: int, name: str = "", payload=b"", what: str = "", tail=None, out=None) -> bytes:
+        """One request/response.  ``tail`` is an optional second payload part (a tensor's buffer,
+        sent straight from its memory); ``out`` an optional writable buffer that receives a response
+        body of exactly its size (a tensor read lands in place, no intermediate copies)."""
         nb = name.encode()
-        self.sock.sendall(struct.pack("<IIIQ", MAGIC, op, len(nb), len(payload)) + nb + payload)
-        hdr = self._recv(12)
-        status, n = struct.unpack("<iQ", hdr)
-        body = self._recv(n) if n else b""
+        tail_len = tail.nbytes if tail is not None else 0
+        self.sock.sendall(struct.pack("<IIIQ", MAGIC, op, len(nb), len(payload) + tail_len) + nb + payload)
+        if tail_len:
+            self.sock.sendall(tail)
+        status, n = struct.unpack("<iQ", self._recv(12))
+        if out is not None and status == ST_OK and n == out.nbytes:
+            self._recv_into(out)
+            body = b""
+        else:
+            body = self._recv(n) if n else b""
+            if out is not None and status == ST_OK:
+                raise PsError(ST_SHAPE, "%s(%s)@%s: %d bytes, expected %d" % (what, name, self.hostport, n, out.nbytes))
         if status == ST_TIMEOUT:
             raise QueueTimeout(status, what or name)
         if status != ST_OK:
             raise PsError(status, "%s(%s)@%s" % (what or "op%d" % op, name, self.hostport))
         return body
 
-    def _recv(self, n: int) -> bytes:
-        buf = bytearray(n)
-        view = memoryview(buf)
-        got = 0
+    def _recv_into(self, view: memoryview) -> None:
+        view = view.cast("B")
+        got, n = 0, view.nbytes
         while got < n:
             r = self.sock.recv_into(view[got:], n - got)
             if r == 0:
                 raise ConnectionError("connection to %s closed" % self.hostport)
             got += r
+
+    def _recv(self, n: int) -> bytes:
+        buf = bytearray(n)
+        self._recv_into(memoryview(buf))
         return bytes(buf)
 
     def close(self) -> None:
@@ -129,11 +148,11 @@ class PsClient:
         return struct.unpack("<I", self._call(OP_VAR_DECLARE, name, p, "declare"))[0] == 1
 
     def var_assign(self, name: str, value: torch.Tensor) -> None:
-        self._call(OP_VAR_ASSIGN, name, value.contiguous().numpy().tobytes(), "assign")
+        self._call(OP_VAR_ASSIGN, name, b"", "assign", tail=_buffer(value))
 
     def var_read(self, name: str, shape: Sequence[int], dtype: torch.dtype) -> torch.Tensor:
-        raw = self._call(OP_VAR_READ, name, b"", "read")
-        arr = np.frombuffer(raw, dtype=_np_dtype(dtype)).reshape(tuple(shape)).copy()
+        arr = np.empty(tuple(shape), dtype=_np_dtype(dtype))
+        self._call(OP_VAR_READ, name, b"", "read", out=memoryview(arr.reshape(-1)))
         return torch.from_numpy(arr)
 
     def uninitialized_count(self) -> int:
@@ -162,9 +181,8 @@ class PsClient:
     def apply(self, name: str, grad: torch.Tensor, kind: int, hyper: Sequence[float],
               slot_names: Sequence[str], beta_powers: Sequence[float] = (0.0, 0.0)) -> None:
         """Async (Hogwild) dense update of ``name`` on its ps."""
-        p = self._apply_header(kind, hyper, beta_powers, slot_names) + \
-            grad.to(torch.float32).contiguous().numpy().tobytes()
-        self._call(OP_APPLY, name, p, "apply")
+        self._call(OP_APPLY, name, self._apply_header(kind, hyper, beta_powers, slot_names), "apply",
+                   tail=_buffer(grad.to(torch.float32)))
 
     # ---- queues --------------------------------------------------------------------
     def queue_create(self, name: str, capacity: int) -> None:
@@ -188,8 +206,9 @@ class PsClient:
 
     def acc_apply(self, name: str, grad: torch.Tensor, local_step: int) -> bool:
         """Returns False when the gradient was stale and dropped."""
-        p = struct.pack("<q", local_step) + grad.to(torch.float32).contiguous().numpy().tobytes()
-        return struct.unpack("<I", self._call(OP_ACC_APPLY, name, p, "acc_apply"))[0] == 1
+        body = self._call(OP_ACC_APPLY, name, struct.pack("<q", local_step), "acc_apply",
+                          tail=_buffer(grad.to(torch.float32)))
+        return struct.unpack("<I", body)[0] == 1
 
     def acc_take_apply(self, name: str, required: int, kind: int, hyper: Sequence[float],
                        slot_names: Sequence[str], beta_powers: Sequence[float] = (0.0, 0.0)) -> int:

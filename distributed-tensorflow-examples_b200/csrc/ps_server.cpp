@@ -301,10 +301,16 @@ void handle(Server* s, int fd) {
                     ok = respond(s, fd, ST_SHAPE);
                     break;
                 }
-                // gradient bytes may be unaligned inside the payload: copy out
-                std::vector<float> g(v->numel());
-                memcpy(g.data(), payload.data() + off, v->data.size());
-                apply_dense(h, reinterpret_cast<float*>(v->data.data()), g.data(),
+                // gradient bytes may be unaligned inside the payload (slot names have any length):
+                // use them in place when they are float-aligned, copy out otherwise
+                const uint8_t* gbytes = payload.data() + off;
+                std::vector<float> gcopy;
+                if (reinterpret_cast<uintptr_t>(gbytes) % alignof(float) != 0) {
+                    gcopy.resize(v->numel());
+                    memcpy(gcopy.data(), gbytes, v->data.size());
+                    gbytes = reinterpret_cast<const uint8_t*>(gcopy.data());
+                }
+                apply_dense(h, reinterpret_cast<float*>(v->data.data()), reinterpret_cast<const float*>(gbytes),
                             slots[0] ? reinterpret_cast<float*>(slots[0]->data.data()) : nullptr,
                             slots[1] ? reinterpret_cast<float*>(slots[1]->data.data()) : nullptr, v->numel(), 1.0f);
                 s->n_applies++;
