@@ -153,6 +153,148 @@ def build_step(model: str, world: int, local: int, dims=None):
     return step
 
 
+def build_graph_step(model: str, world: int, local: int, dims, static_batch):
+    """The strongest form of the baseline: the WHOLE step -- forward, backward, one flat NCCL
+    all-reduce of the gradients, optimizer -- captured once in a CUDA graph and replayed, so it pays
+    one launch per step like the product arm does.  cuBLAS/cuDNN kernels, bf16 autocast, capturable
+    torch.optim optimizers.  Returns (replay_fn, static loss tensor)."""
+    import torch.distributed as dist
+    if model == "encoder":
+        nets = [AE().cuda()]
+        opts = [torch.optim.RMSprop(nets[0].parameters(), lr=0.01, alpha=0.9, eps=1e-10, capturable=True)]
+
+        def fwd_bwd(b):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = nets[0](b["x"])
+            loss.backward()
+            return loss
+    elif model == "lstm":
+        nets = [LSTMNet().cuda()]
+        opts = [torch.optim.SGD(nets[0].parameters(), lr=0.001)]
+
+        def fwd_bwd(b):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                loss = nets[0](b["x"], b["y"])
+            loss.backward()
+            return loss
+    elif model == "scaled_lstm":
+        nets = [StackedLSTM(dims["num_hidden"], dims["num_layers"]).to(torch.bfloat16).cuda()]
+        opts = [torch.optim.SGD(nets[0].parameters(), lr=0.001)]
+
+        def fwd_bwd(b):
+            loss = nets[0](b["x"].to(torch.bfloat16), b["y"])
+            loss.backward()
+            return loss
+    else:
+        g, d = G().cuda(), D().cuda()
+        nets = [g, d]
+        opts = [torch.optim.Adam(g.parameters(), lr=2e-4, capturable=True),
+                torch.optim.Adam(d.parameters(), lr=2e-4, capturable=True)]
+        g_params, d_params = list(g.parameters()), list(d.parameters())
+
+        def fwd_bwd(b):
+            with torch.autocast("cuda", dtype=torch.bfloat16):
+                fake = g(b["z"])
+                l_real = d(b["x"]).float()
+                l_fake = d(fake).float()
+                gen_loss = F.softplus(-l_fake).mean()
+                disc_loss = (F.softplus(-l_real) + F.softplus(l_fake)).mean()
+            gen_loss.backward(inputs=g_params, retain_graph=True)
+            disc_loss.backward(inputs=d_params)
+            return gen_loss + disc_loss
+    params = [p for n in nets for p in n.parameters()]
+    # gradients live in ONE flat buffer (params' .grad are views): one all-reduce, no bucket copies
+    flat = torch.zeros(sum(p.numel() for p in params), device="cuda", dtype=params[0].dtype)
+    o = 0
+    for p in params:
+        p.grad = flat[o:o + p.numel()].view_as(p)
+        o += p.numel()
+
+    def body():
+        flat.zero_()
+        loss = fwd_bwd(static_batch)
+        if world > 1:
+            dist.all_reduce(flat, op=dist.ReduceOp.AVG)
+        for opt in opts:
+            opt.step()
+        return loss
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            body()
+    torch.cuda.current_stream().wait_stream(side)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        static_loss = body()
+    torch.cuda.synchronize()
+    return graph.replay, static_loss
+
+
+def run_graph(args, rank, world, local, bench, keep_group: bool = False):
+    """``--impl torch_ddp_graph``: the CUDA-graphed baseline, timed exactly like the product arm."""
+    model = args.model
+    B = args.batch or bench.PER_GPU_BATCH[model]
+    dims = None
+    if model == "scaled_lstm":
+        dims = dict(num_input=args.hidden, timesteps=args.seq, num_hidden=args.hidden, num_layers=args.layers)
+    batches = bench.synthetic_batches(model, B, 2 if dims else 8, args.seed * 1000 + rank, dims)
+    dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
+    static = {k: v.clone() for k, v in dev_batches[0].items()}
+    replay, static_loss = build_graph_step(model, world, local, dims, static)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    host_loss = torch.zeros(1).pin_memory()
+
+    def dev_step(i):
+        for k, v in dev_batches[i % len(dev_batches)].items():
+            static[k].copy_(v, non_blocking=True)
+        replay()
+
+    def e2e_step(i):
+        for k, v in batches[i % len(batches)].items():
+            static[k].copy_(v, non_blocking=True)               # pinned host -> device
+        replay()
+        host_loss.copy_(static_loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    for i in range(args.warmup):
+        dev_step(i)
+    torch.cuda.synchronize()
+    sampler = bench.ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = bench.timed_device_steps(dev_step, args.steps, world, flush)
+    for i in range(args.warmup):
+        e2e_step(i)
+    ms_e2e = bench.timed_e2e_steps(e2e_step, args.steps, world)
+    clocks = sampler.stop() if rank == 0 else None
+    res = None
+    if rank == 0:
+        total = B * world * args.steps
+        res = {"metric": "examples/sec", "value": round(total / (ms / 1e3), 1), "unit": "examples/s",
+               "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+               "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "bf16 autocast", "data": "synthetic MNIST-shaped, random-init weights",
+               "impl": "torch_ddp_graph",
+               "config": {"model": bench.MODEL_LABEL[model], "global_batch": B * world,
+                          "parallelism": "dp%d, whole step in one CUDA graph, flat NCCL all-reduce" % world,
+                          "l2": "flushed between timed iterations (256 MiB write outside the event pairs)",
+                          "cuda_graph": True},
+               "clocks": clocks,
+               "e2e": {"value": round(total / (ms_e2e / 1e3), 1), "unit": "examples/s",
+                       "ms_per_step": round(ms_e2e / args.steps, 4),
+                       "h2d_bytes_per_step": sum(v.numel() * 4 for v in batches[0].values()),
+                       "d2h_bytes_per_step": 4},
+               "gpu_launches": 0, "final_loss": float(static_loss)}
+    if world > 1 and not keep_group:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+    return res
+
+
 def run(args, rank, world, local, bench):
     model = args.model
     B = args.batch or bench.PER_GPU_BATCH[model]

@@ -4,8 +4,12 @@
 rows (28 steps x 28 features) sync mode"), one rank per GPU, weak scaling (128 examples per
 GPU per step, lstm:29).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--model lstm|gan|encoder]
-                    [--mode sync|async] [--impl psb200|reference|torch_ddp]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--model lstm|gan|encoder|scaled_lstm]
+                    [--mode sync|async] [--impl psb200|reference|torch_ddp|torch_ddp_graph]
+
+The product arm also runs the strongest baseline (PyTorch + cuBLAS/cuDNN + NCCL, the whole step
+captured in one CUDA graph: ``baseline/torch_ddp.py``) in the SAME invocation -- same lease, same
+clocks -- and reports it under ``baseline_same_run``; ``vs_baseline`` is computed from that run.
 
 For N > 1 launch with ``python -m torch.distributed.run --nproc-per-node N ... bench.py
 --gpus N ...``.  Rank 0 prints ONE JSON line.
@@ -158,7 +162,8 @@ def run_psb200(args):
     if model == "scaled_lstm":
         dims = dict(num_input=args.hidden, timesteps=args.seq, num_hidden=args.hidden, num_layers=args.layers)
     tr = DeviceTrainer(model, rank, world, group, mode=args.mode, seed=args.seed, batch=B,
-                       gan_update=args.gan_update, plan_kwargs=kw, model_kwargs=dims, bcast=bool(args.bcast))
+                       gan_update=args.gan_update, plan_kwargs=kw, model_kwargs=dims, bcast=bool(args.bcast),
+                       partition=bool(args.partition))
     tr.initialize()
     batches = synthetic_batches(model, B, 2 if model == "scaled_lstm" else 8, args.seed * 1000 + rank, dims)
     dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
@@ -201,14 +206,31 @@ def run_psb200(args):
     tr.drain()
     ms_e2e = timed_e2e_steps(e2e_pipelined, args.steps, world)
     clocks = sampler.stop() if rank == 0 else None
+    used_graph = tr.graph is not None
+    h2d_bytes, d2h_bytes = tr.h2d_bytes_per_step(batches[0]), tr.d2h_bytes_per_step()
     last = tr.step(batches[0])
     gstep = last["global_step"]
+    tr.close()
+    del tr, dev_batches, flush
+    torch.cuda.empty_cache()
+    # ---- the baseline arm, same process, same GPUs, right after the product arm
+    base_run, base_err = None, None
+    if args.baseline:
+        try:
+            from baseline.torch_ddp import run_graph
+            base_run = run_graph(args, rank, world, local, sys.modules[__name__], keep_group=True)
+        except Exception as e:      # the product number stands on its own; say why the ratio is missing
+            base_err = "%s: %s" % (type(e).__name__, str(e)[:200])
     result = None
     if rank == 0:
         total = B * world * args.steps
         value = total / (ms / 1e3)
         e2e = total / (ms_e2e / 1e3)
-        base = _measured_baseline(model, world)
+        base = base_run["value"] if base_run else None
+        base_label = "PyTorch cuBLAS/cuDNN + NCCL, whole step in one CUDA graph, measured in this run"
+        if base is None:
+            base = _measured_baseline(model, world)
+            base_label = "EAGER PyTorch DDP rendition from baseline/measured.json (stored, other lease)" if base else None
         result = {
             "metric": "examples/sec", "value": round(value, 1), "unit": "examples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4),
@@ -220,12 +242,12 @@ def run_psb200(args):
                        "global_batch": B * world, "seq_len": 28 if model == "lstm" else (args.seq if dims else None),
                        "parallelism": "dp%d ps-sharded (%s%s)" % (world, args.mode, "" if args.bcast else ", pull-fused"),
                        "l2": "flushed between timed iterations (256 MiB write outside the event pairs)",
-                       "cuda_graph": tr.graph is not None,
-                       "baseline_for_vs": "PyTorch DDP/NCCL rendition, baseline/measured.json" if base else None},
+                       "cuda_graph": used_graph,
+                       "baseline_for_vs": base_label},
             "clocks": clocks,
             "e2e": {"value": round(e2e, 1), "unit": "examples/s", "ms_per_step": round(ms_e2e / args.steps, 4),
-                    "h2d_bytes_per_step": tr.h2d_bytes_per_step(batches[0]),
-                    "d2h_bytes_per_step": tr.d2h_bytes_per_step(),
+                    "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": d2h_bytes,
                     "api": "DeviceTrainer.step_async: every step copies its batch from pinned host memory and "
                            "reads loss+global_step back; submission of step i+1 overlaps step i",
                     "blocking_api_value": round(total / (ms_e2e_sync / 1e3), 1),
@@ -234,7 +256,11 @@ def run_psb200(args):
             "push_pull_us_per_step": {k: round(v, 2) for k, v in push_prof.items() if k != "calls"},
             "final": {"global_step": gstep, "losses": {k: v for k, v in last.items() if k != "global_step"}},
         }
-    tr.close()
+        if base_run:
+            result["baseline_same_run"] = {k: base_run[k] for k in ("impl", "value", "ms_per_step", "e2e", "clocks", "dtype")}
+            result["e2e"]["vs_baseline_e2e"] = round(e2e / base_run["e2e"]["value"], 3)
+        elif base_err:
+            result["baseline_same_run"] = {"unavailable": base_err}
     if world > 1:
         import torch.distributed as dist
         dist.barrier()
@@ -261,9 +287,10 @@ def run_reference(args):
 
 
 def run_torch_ddp(args):
-    from baseline.torch_ddp import run as run_ddp
+    from baseline.torch_ddp import run as run_ddp, run_graph
     rank, world, local, group = _dist_setup(args.gpus)
-    return run_ddp(args, rank, world, local, sys.modules[__name__])
+    fn = run_graph if args.impl == "torch_ddp_graph" else run_ddp
+    return fn(args, rank, world, local, sys.modules[__name__])
 
 
 def main():
@@ -278,7 +305,9 @@ def main():
     ap.add_argument("--batch", type=int, default=0, help="per-GPU batch (0 = the model's reference value)")
     ap.add_argument("--mode", default="sync", choices=["sync", "async"])
     ap.add_argument("--gan_update", default="simultaneous", choices=["simultaneous", "alternating"])
-    ap.add_argument("--impl", default="psb200", choices=["psb200", "reference", "torch_ddp"])
+    ap.add_argument("--impl", default="psb200", choices=["psb200", "reference", "torch_ddp", "torch_ddp_graph"])
+    ap.add_argument("--baseline", type=int, default=1, help="1: also run the CUDA-graphed PyTorch baseline in this invocation")
+    ap.add_argument("--partition", type=int, default=1, help="1: big variables are split in row blocks over all ranks")
     ap.add_argument("--bcast", type=int, default=1, help="1: push kernel refreshes every rank's arena; 0: consumers pull from the owner")
     ap.add_argument("--seed", type=int, default=0)
     args = ap.parse_args()

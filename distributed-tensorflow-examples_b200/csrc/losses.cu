@@ -29,10 +29,14 @@ __device__ __forceinline__ float softplus(float x) {
 // in fp32 [M, N] (ld_in) -> out bf16 [M, ld_out] and/or out_t bf16 [N, ld_t]; 32x32 tiles.
 __global__ void __launch_bounds__(256) cast_transpose_kernel(const float* __restrict__ in, int ld_in, int M, int N,
                                                              __nv_bfloat16* out, int ld_out,
-                                                             __nv_bfloat16* out_t, int ld_t) {
+                                                             __nv_bfloat16* out_t, int ld_t,
+                                                             float* clear, int n_clear) {
     __shared__ float tile[32][33];
     const int n0 = blockIdx.x * 32, m0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
+    // first kernel of a step: also resets the accumulators later kernels add into (loss scalars)
+    if (clear != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && static_cast<int>(threadIdx.x) < n_clear)
+        clear[threadIdx.x] = 0.0f;
 #pragma unroll
     for (int r = ty; r < 32; r += 8) {
         const int m = m0 + r, n = n0 + tx;
@@ -254,8 +258,21 @@ extern "C" int psb_cast_transpose(const float* in, int ld_in, int M, int N, void
     const int ncols = out ? (ld_out > N ? ld_out : N) : N;
     dim3 grid((ncols + 31) / 32, (M + 31) / 32);
     cast_transpose_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
-        in, ld_in, M, N, static_cast<__nv_bfloat16*>(out), ld_out, static_cast<__nv_bfloat16*>(out_t), ld_t);
+        in, ld_in, M, N, static_cast<__nv_bfloat16*>(out), ld_out, static_cast<__nv_bfloat16*>(out_t), ld_t, nullptr, 0);
     return after_launch("cast_transpose");
+}
+
+extern "C" int psb_cast_transpose_clear(const float* in, int ld_in, int M, int N, void* out, int ld_out,
+                                        void* out_t, int ld_t, float* clear, int n_clear, void* stream) {
+    using namespace psb;
+    if (!in || M < 1 || N < 1 || (!out && !out_t)) return fail(PSB_ERR_ARG, "psb_cast_transpose_clear: bad argument");
+    if (n_clear < 0 || n_clear > 256 || (n_clear > 0 && !clear))
+        return fail(PSB_ERR_ARG, "psb_cast_transpose_clear: clear at most 256 floats");
+    const int ncols = out ? (ld_out > N ? ld_out : N) : N;
+    dim3 grid((ncols + 31) / 32, (M + 31) / 32);
+    cast_transpose_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        in, ld_in, M, N, static_cast<__nv_bfloat16*>(out), ld_out, static_cast<__nv_bfloat16*>(out_t), ld_t, clear, n_clear);
+    return after_launch("cast_transpose_clear");
 }
 
 extern "C" int psb_mse_sigmoid_grad(const float* y, int ld_y, const float* x, int ld_x, int M, int N,

@@ -52,6 +52,7 @@ enum Status : int32_t {
 };
 
 constexpr uint32_t kMagic = 0x31425350;  // "PSB1"
+constexpr uint64_t kMaxNumel = 1ull << 32;  // elements per variable a declare may ask for (16 GiB of fp32)
 
 struct Variable {
     uint32_t dtype = 0;  // 0 f32, 1 i32
@@ -179,7 +180,8 @@ size_t parse_apply(Server* s, const std::vector<uint8_t>& p, ApplyHdr* h, Variab
     if (p.size() < sizeof(ApplyHdr)) return 0;
     memcpy(h, p.data(), sizeof(ApplyHdr));
     size_t off = sizeof(ApplyHdr);
-    if (h->nslots > 2) return 0;
+    // SGD carries no slots, RMSProp and Adam exactly two (rms, momentum | m, v)
+    if (h->kind > 2 || h->nslots != (h->kind == 0 ? 0u : 2u)) return 0;
     for (uint32_t k = 0; k < h->nslots; ++k) {
         if (off + 4 > p.size()) return 0;
         uint32_t len;
@@ -189,9 +191,17 @@ size_t parse_apply(Server* s, const std::vector<uint8_t>& p, ApplyHdr* h, Variab
         std::string name(reinterpret_cast<const char*>(p.data() + off), len);
         off += len;
         slots[k] = s->find_var(name);
-        if (!slots[k]) return 0;
+        if (!slots[k] || slots[k]->dtype != 0) return 0;
     }
     return off;
+}
+
+// Every slot a kind needs is present and as large as the variable it belongs to.
+bool slots_fit(const ApplyHdr& h, Variable* const* slots, const Variable* v) {
+    if (v->dtype != 0) return false;
+    for (uint32_t k = 0; k < h.nslots; ++k)
+        if (!slots[k] || slots[k]->data.size() != v->data.size()) return false;
+    return true;
 }
 
 void handle(Server* s, int fd) {
@@ -215,6 +225,7 @@ void handle(Server* s, int fd) {
         s->n_requests++;
         s->bytes_in += 20 + name_len + plen;
         bool ok = true;
+        try {
         switch (op) {
             case OP_PING:
                 ok = respond(s, fd, ST_OK);
@@ -227,10 +238,13 @@ void handle(Server* s, int fd) {
                 if (plen != 8 + 8ull * ndim || ndim > 8) { ok = respond(s, fd, ST_BAD_REQUEST); break; }
                 std::vector<uint64_t> dims(ndim);
                 uint64_t numel = 1;
+                bool too_big = false;
                 for (uint32_t i = 0; i < ndim; ++i) {
                     memcpy(&dims[i], payload.data() + 8 + 8 * i, 8);
-                    numel *= dims[i];
+                    if (dims[i] > kMaxNumel || (dims[i] != 0 && numel > kMaxNumel / dims[i])) too_big = true;
+                    else numel *= dims[i];
                 }
+                if (too_big || dtype > 1) { ok = respond(s, fd, ST_BAD_REQUEST); break; }
                 uint32_t inited = 0;
                 int32_t st = ST_OK;
                 {
@@ -296,11 +310,7 @@ void handle(Server* s, int fd) {
                 Variable* slots[2] = {nullptr, nullptr};
                 size_t off = parse_apply(s, payload, &h, slots);
                 if (!off || payload.size() - off != v->data.size()) { ok = respond(s, fd, ST_BAD_REQUEST); break; }
-                if ((h.kind != 0 && h.nslots != 2) || (h.nslots && (slots[0]->data.size() != v->data.size() ||
-                                                                    slots[1]->data.size() != v->data.size()))) {
-                    ok = respond(s, fd, ST_SHAPE);
-                    break;
-                }
+                if (!slots_fit(h, slots, v)) { ok = respond(s, fd, ST_SHAPE); break; }
                 // gradient bytes may be unaligned inside the payload (slot names have any length):
                 // use them in place when they are float-aligned, copy out otherwise
                 const uint8_t* gbytes = payload.data() + off;
@@ -452,6 +462,8 @@ void handle(Server* s, int fd) {
                 ApplyHdr h;
                 Variable* slots[2] = {nullptr, nullptr};
                 if (!parse_apply(s, rest, &h, slots)) { ok = respond(s, fd, ST_BAD_REQUEST); break; }
+                if (!v->initialized.load()) { ok = respond(s, fd, ST_UNINITIALIZED); break; }
+                if (!slots_fit(h, slots, v) || a->sum.size() != v->numel()) { ok = respond(s, fd, ST_SHAPE); break; }
                 uint32_t used = 0;
                 int32_t st = ST_OK;
                 {
@@ -468,6 +480,10 @@ void handle(Server* s, int fd) {
                                     v->numel(), 1.0f / static_cast<float>(used));
                         std::fill(a->sum.begin(), a->sum.end(), 0.0f);
                         a->count = 0;
+                        // the accumulator's step advances WITH the take (TF's ConditionalAccumulator does the
+                        // same inside TakeGrad): a backup worker's gradient computed on the old parameters
+                        // that arrives from now on is stale and dropped, not averaged into the next step
+                        a->global_step += 1;
                         s->n_applies++;
                     }
                 }
@@ -481,7 +497,7 @@ void handle(Server* s, int fd) {
                 memcpy(&step, payload.data(), 8);
                 {
                     std::lock_guard<std::mutex> l(a->mu);
-                    a->global_step = step;
+                    if (step > a->global_step) a->global_step = step;   // the take already advanced it by one
                 }
                 ok = respond(s, fd, ST_OK);
                 break;
@@ -503,7 +519,18 @@ void handle(Server* s, int fd) {
             default:
                 ok = respond(s, fd, ST_BAD_REQUEST);
         }
+        } catch (const std::exception&) {
+            // bad_alloc / length_error from a hostile size: answer, keep the process alive
+            ok = respond(s, fd, ST_BAD_REQUEST);
+        }
         if (!ok) break;
+    }
+    {
+        // forget the descriptor BEFORE closing it: psb_ps_stop must never shut down a number the
+        // process has meanwhile reused for something else
+        std::lock_guard<std::mutex> l(s->conn_mu);
+        for (size_t i = 0; i < s->conn_fds.size(); ++i)
+            if (s->conn_fds[i] == fd) { s->conn_fds[i] = s->conn_fds.back(); s->conn_fds.pop_back(); break; }
     }
     ::close(fd);
 }

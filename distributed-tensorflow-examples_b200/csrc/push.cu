@@ -1,12 +1,13 @@
 // Gradient push fused with the owner-side optimizer update, over NVLink peer memory.
 //
 // Every rank keeps its gradients of ALL variables in one flat fp32 buffer that its peers
-// can address (CUDA IPC).  The rank that owns a variable ("its ps shard") runs this kernel
-// over the variable's segment:
+// can address (CUDA IPC).  The rank that owns a variable -- or a row block of one: big
+// variables are split over all ranks -- ("its ps shard") runs this kernel over the segment:
 //
-//   wait until every rank has published "gradients of step s are complete"   (signal pads)
-//   g      = (sum over ranks r of grad_r[i]) * inv_replicas     -- P2P 128-bit loads, fixed
-//                                                                   rank order (deterministic)
+//   wait until every rank (or the first R of N) has published "gradients of step s are
+//   complete"                                                            (signal pads)
+//   g      = (sum over contributing ranks r of grad_r[i]) / contributors -- P2P 128-bit loads,
+//            all ranks' loads in flight together, summed in rank order (deterministic)
 //   w,slots = optimizer(w, slots, g)                             -- SGD / RMSProp / Adam, fp32
 //   bf16 compute copies of w (natural and transposed layout) written to the owner's arena,
 //   or to every rank's arena (push-mode all-gather) when `bcast` is set
@@ -15,9 +16,21 @@
 //
 // i.e. reduce-scatter + optimizer apply (+ all-gather) in ONE kernel, no NCCL and no
 // intermediate reduced-gradient buffer.  With world == 1 the same kernel is the plain
-// local optimizer step.  In async (Hogwild) mode a worker launches it with world == 1 and
-// `master`/`slot` pointers that live in the OWNER's HBM: the update is then a lock-free
-// remote read-modify-write, and SGD degenerates to a peer atomic add.
+// local optimizer step.
+//
+// The same kernel also serves the decoupled ps role (csrc/ps_service.cu): launched with
+// PSB_PUSH_TRY_GRADS it looks at the pads once, applies only if enough gradients have
+// arrived (sync, R of N: late gradients are never read -- they are stale) or applies every
+// newly arrived gradient on its own and acknowledges its sender (async, PSB_PUSH_EACH),
+// and returns without ever spinning.  Workers then only signal and wait (psb_push_commit).
+//
+// In the legacy async mode a worker launches it with world == 1 and `master`/`slot`
+// pointers that live in the OWNER's HBM: a lock-free remote read-modify-write; SGD
+// degenerates to a peer atomic add.
+//
+// Every cross-GPU wait is bounded: a %globaltimer deadline (timeout_ns) and a host-settable
+// abort word end the spin, the kernel records why in local_ctrl[3] and finishes without
+// applying; the trainer turns that into an exception instead of a hung GPU.
 //
 // ref: Optimizer.minimize -> Send(grad) -> Apply{GradientDescent,RMSProp,Adam} on the ps +
 //      AssignAdd(global_step): encoder:137, gan:158-159, lstm:97; sync aggregation per
@@ -31,8 +44,23 @@
 namespace psb {
 
 constexpr int kPushThreads = 256;
+constexpr int kMaxWorld = 16;
 constexpr int kPadGrads = 0;      // pad[kPadGrads + r]  : rank r's gradients for step >= value are complete
 constexpr int kPadParams = 16;    // pad[kPadParams + r] : rank r has applied step >= value
+constexpr int kPadAck = 32;       // pad[kPadAck + r]    : owner r has consumed this rank's gradient number `value` (async)
+
+// words of local_ctrl (PSB_PUSH_CTRL_WORDS of them, zero-initialised by the caller)
+enum : int {
+    kCtrlGo = 0,        // launch sequence number block (0,0) publishes once it has decided the contributor mask
+    kCtrlDone = 1,      // finished-block counter
+    kCtrlStep = 2,      // last applied step token
+    kCtrlStatus = 3,    // 0 ok | PSB_PUSH_ST_*: sticky until the host clears it
+    kCtrlAbort = 4,     // host writes non-zero: every spin ends, status = PSB_PUSH_ST_ABORTED
+    kCtrlMask = 5,      // contributor mask of this launch (0 = nothing applied)
+    kCtrlSeq = 6,       // launches completed
+    kCtrlApplied = 7,   // aggregates / gradients applied so far (tests, service statistics)
+    kCtrlConsumed = 8,  // [8 .. 8+16): async, last gradient number consumed per rank
+};
 
 struct PushArgs {
     const psb_push_seg_t* segs;
@@ -45,14 +73,16 @@ struct PushArgs {
     int n_arenas;                      // entries of arena_ptrs/farena_ptrs written when bcast
     float inv_replicas;
     uint32_t step_id;                  // 0 = take local_ctrl[2] + 1
-    uint32_t* local_ctrl;              // [0] go flag, [1] finished-block counter, [2] last step id
+    uint32_t* local_ctrl;
     psb_beta_update_t beta[2];
     int nbeta;
     int32_t* global_step;
     int step_delta;
     int async_sgd_atomic;              // 1: SGD segments use atomicAdd on master (peer atomics)
-    int signal_params;                 // 1: publish params-ready to peers at the end
+    int phases;                        // PSB_PUSH_* bits
+    int replicas;                      // gradients to aggregate (R of N); <= 0 or >= world: all
     unsigned long long* prof;          // optional [8]: t0, t1, -, -, sum(wait grads), sum(apply), sum(wait params), calls
+    unsigned long long timeout_ns;     // 0 = wait forever
 };
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -61,19 +91,75 @@ __device__ __forceinline__ unsigned long long global_ns() {
     return t;
 }
 
-// L2-coherent (L1-bypassing) 128-bit load; no "memory" clobber so independent loads can be
-// batched — ordering against the flag wait comes from the __syncthreads() after it.
-__device__ __forceinline__ float4 ld_volatile_v4(const float* p) {
+// L2-coherent (L1-bypassing) loads; no "memory" clobber so independent loads can be
+// batched -- ordering against the flag wait comes from the __syncthreads() after it.
+__device__ __forceinline__ float4 ld_cg_v4(const float* p) {
     float4 r;
     asm volatile("ld.global.cg.v4.f32 {%0,%1,%2,%3}, [%4];"
                  : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
                  : "l"(p));
     return r;
 }
-__device__ __forceinline__ float ld_volatile_f32(const float* p) {
+__device__ __forceinline__ float ld_cg_f32(const float* p) {
     float r;
     asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(r) : "l"(p));
     return r;
+}
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
+    uint32_t r;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
+    return r;
+}
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// Four consecutive floats: one 128-bit access when the group is whole and aligned, otherwise
+// `nvalid` scalar ones (rows whose length is not a multiple of four, the tail of a vector).
+__device__ __forceinline__ float4 ld4_cg(const float* p, bool v4, int nvalid) {
+    if (v4) return ld_cg_v4(p);
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (nvalid > 0) r.x = ld_cg_f32(p);
+    if (nvalid > 1) r.y = ld_cg_f32(p + 1);
+    if (nvalid > 2) r.z = ld_cg_f32(p + 2);
+    if (nvalid > 3) r.w = ld_cg_f32(p + 3);
+    return r;
+}
+__device__ __forceinline__ float4 ld4(const float* p, bool v4, int nvalid) {
+    if (v4) return *reinterpret_cast<const float4*>(p);
+    float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (nvalid > 0) r.x = p[0];
+    if (nvalid > 1) r.y = p[1];
+    if (nvalid > 2) r.z = p[2];
+    if (nvalid > 3) r.w = p[3];
+    return r;
+}
+__device__ __forceinline__ void st4(float* p, const float4& v, bool v4, int nvalid) {
+    if (v4) { *reinterpret_cast<float4*>(p) = v; return; }
+    if (nvalid > 0) p[0] = v.x;
+    if (nvalid > 1) p[1] = v.y;
+    if (nvalid > 2) p[2] = v.z;
+    if (nvalid > 3) p[3] = v.w;
+}
+
+struct Spin {
+    const uint32_t* abort_word;
+    unsigned long long timeout_ns;
+};
+
+// Wait until *flag >= want (wrap-safe).  0 = seen, otherwise the PSB_PUSH_ST_* reason it gave up.
+__device__ __forceinline__ int spin_flag(const uint32_t* flag, uint32_t want, const Spin& sp, int timeout_code) {
+    unsigned long long t0 = 0;
+    uint32_t it = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(flag) - want) < 0) {
+        if ((++it & 1023u) == 0) {
+            if (ld_volatile_u32(sp.abort_word) != 0) return PSB_PUSH_ST_ABORTED;
+            if (sp.timeout_ns != 0) {
+                const unsigned long long now = global_ns();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > sp.timeout_ns) return timeout_code;
+            }
+        }
+    }
+    return 0;
 }
 
 struct OptCtx {
@@ -95,156 +181,240 @@ __device__ __forceinline__ float apply_val(const OptCtx& o, float w, float g, fl
     return w - o.lr_t * s0 / (sqrtf(s1) + o.eps);
 }
 
-__global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
+// The gradient of one group of four elements from every contributing rank (t[r], loaded by the
+// caller with all loads in flight) applied to w/v0/v1: the mean in one optimizer step (sync), or
+// one optimizer step per rank (async, `each`).
+template <int MAXW>
+__device__ __forceinline__ void apply4(const OptCtx& o, const float4 (&t)[MAXW], int world, uint32_t mask, bool each, float inv,
+                                       float4& w, float4& v0, float4& v1) {
+    if (!each) {
+        float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int r = 0; r < MAXW; ++r)
+            if (r < world && ((mask >> r) & 1u)) { g.x += t[r].x; g.y += t[r].y; g.z += t[r].z; g.w += t[r].w; }
+        w.x = apply_val(o, w.x, g.x * inv, v0.x, v1.x);
+        w.y = apply_val(o, w.y, g.y * inv, v0.y, v1.y);
+        w.z = apply_val(o, w.z, g.z * inv, v0.z, v1.z);
+        w.w = apply_val(o, w.w, g.w * inv, v0.w, v1.w);
+    } else {
+#pragma unroll
+        for (int r = 0; r < MAXW; ++r)
+            if (r < world && ((mask >> r) & 1u)) {
+                w.x = apply_val(o, w.x, t[r].x, v0.x, v1.x);
+                w.y = apply_val(o, w.y, t[r].y, v0.y, v1.y);
+                w.z = apply_val(o, w.z, t[r].z, v0.z, v1.z);
+                w.w = apply_val(o, w.w, t[r].w, v0.w, v1.w);
+            }
+    }
+}
+
+// Templated on the largest world the register-resident batch of peer loads is sized for.
+template <int MAXW>
+__global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a) {
+    __shared__ const float* s_grad[kMaxWorld];
+    __shared__ __nv_bfloat16* s_arena[kMaxWorld];
+    __shared__ float* s_farena[kMaxWorld];
+    __shared__ int s_bad;
+    __shared__ uint32_t s_mask;
+    __shared__ bool is_last;
+    __shared__ __nv_bfloat16 tile[2][32][34];
+
     const int tid = threadIdx.x;
     const bool first_block = blockIdx.x == 0 && blockIdx.y == 0;
     const uint32_t total_blocks = gridDim.x * gridDim.y;
-    const bool auto_step = a.step_id == 0;
-    if (auto_step) a.step_id = *reinterpret_cast<volatile uint32_t*>(a.local_ctrl + 2) + 1;
+    uint32_t* const ctrl = a.local_ctrl;
+    const Spin sp{ctrl + kCtrlAbort, a.timeout_ns};
 
-    if (a.prof != nullptr && first_block && tid == 0) a.prof[0] = global_ns();
-    // ---------------- cross-GPU: all gradients of this step are in place
-    if (a.world > 1) {
-        if (first_block) {
-            if (tid < a.world) {
-                __threadfence_system();
-                st_release_sys(a.pad_ptrs[tid] + kPadGrads + a.rank, a.step_id);
-                const uint32_t* mine = a.pad_ptrs[a.rank] + kPadGrads + tid;
-                while (static_cast<int32_t>(ld_acquire_sys(mine) - a.step_id) < 0) {
-                }
-            }
-            __syncthreads();
-            if (tid == 0) {
-                if (a.prof != nullptr) a.prof[1] = global_ns();
-                __threadfence();
-                atomicExch(a.local_ctrl, a.step_id);
-            }
-        } else {
-            if (tid == 0) {
-                while (static_cast<int32_t>(atomicAdd(a.local_ctrl, 0u) - a.step_id) < 0) {
-                }
-                __threadfence_system();
-            }
-            __syncthreads();
+    // ---------------- prologue on static data only: overlaps the tail of the kernel launched
+    // before this one (programmatic dependent launch)
+    const bool has_seg = static_cast<int>(blockIdx.y) < a.nseg;
+    psb_push_seg_t s;
+    if (has_seg) s = a.segs[blockIdx.y];
+    uint32_t nb = 0;
+    if (has_seg) nb = (s.nblocks != 0 && s.nblocks < gridDim.x) ? s.nblocks : gridDim.x;
+    const bool has_work = has_seg && blockIdx.x < nb && (a.phases & PSB_PUSH_APPLY);
+    if (tid < kMaxWorld) {
+        if (tid < a.world) s_grad[tid] = a.grad_ptrs[tid];
+        if (tid < a.n_arenas) {
+            s_arena[tid] = static_cast<__nv_bfloat16*>(a.arena_ptrs[tid]);
+            s_farena[tid] = a.farena_ptrs[tid];
         }
     }
+    if (tid == 0) { s_bad = 0; s_mask = 0; }
+    uint32_t* my_pad = nullptr;
+    if (a.world > 1) my_pad = a.pad_ptrs[a.rank];
+    griddep_wait();
 
-    // ---------------- reduce + apply + cast for this block's segment
-    if (static_cast<int>(blockIdx.y) < a.nseg) {
-        const psb_push_seg_t s = a.segs[blockIdx.y];
+    const bool auto_step = a.step_id == 0;
+    if (auto_step) a.step_id = ld_volatile_u32(ctrl + kCtrlStep) + 1;
+    const uint32_t seq = ld_volatile_u32(ctrl + kCtrlSeq) + 1;       // this launch
+    const bool each = (a.phases & PSB_PUSH_EACH) != 0;
+    const bool all_ranks = !each && (a.replicas <= 0 || a.replicas >= a.world);
+    uint32_t mask = a.world >= 32 ? 0xffffffffu : ((1u << a.world) - 1u);
+    float inv = a.inv_replicas;
+    __syncthreads();
+
+    if (a.prof != nullptr && first_block && tid == 0) a.prof[0] = global_ns();
+    // ---------------- cross-GPU: the gradients this launch consumes are in place
+    if (a.world > 1) {
+        if (first_block && (a.phases & PSB_PUSH_SIGNAL_GRADS) && tid < a.world) {
+            __threadfence_system();
+            st_release_sys(a.pad_ptrs[tid] + kPadGrads + a.rank, a.step_id);
+        }
+        if (all_ranks && (a.phases & PSB_PUSH_WAIT_GRADS)) {
+            // every block watches the pad itself: no hop through a block-0 "go" flag
+            if ((has_work || first_block) && tid < a.world) {
+                const int bad = spin_flag(my_pad + kPadGrads + tid, a.step_id, sp, PSB_PUSH_ST_TIMEOUT_GRADS);
+                if (bad) atomicMax(&s_bad, bad);
+            }
+        } else if (a.phases & (PSB_PUSH_WAIT_GRADS | PSB_PUSH_TRY_GRADS)) {
+            // R of N / async: block (0,0) decides which gradients this launch takes, everybody follows
+            if (first_block) {
+                if (tid == 0) {
+                    uint32_t m = 0;
+                    int bad = 0;
+                    unsigned long long t0 = 0;
+                    for (uint32_t it = 0;; ++it) {
+                        m = 0;
+                        for (int r = 0; r < a.world; ++r) {
+                            const uint32_t f = ld_acquire_sys(my_pad + kPadGrads + r);
+                            const bool in = each ? (static_cast<int32_t>(f - ld_volatile_u32(ctrl + kCtrlConsumed + r)) > 0)
+                                                 : (static_cast<int32_t>(f - a.step_id) >= 0);
+                            if (in) m |= 1u << r;
+                        }
+                        if (__popc(m) >= (each ? 1 : a.replicas)) break;
+                        m = 0;
+                        if (a.phases & PSB_PUSH_TRY_GRADS) break;
+                        if ((it & 255u) == 255u) {
+                            if (ld_volatile_u32(sp.abort_word) != 0) { bad = PSB_PUSH_ST_ABORTED; break; }
+                            if (sp.timeout_ns != 0) {
+                                const unsigned long long now = global_ns();
+                                if (t0 == 0) t0 = now;
+                                else if (now - t0 > sp.timeout_ns) { bad = PSB_PUSH_ST_TIMEOUT_GRADS; break; }
+                            }
+                        }
+                    }
+                    if (each && m != 0) {
+                        // remember WHICH gradient of each rank this is: acknowledged at the end
+                        for (int r = 0; r < a.world; ++r)
+                            if ((m >> r) & 1u) ctrl[kCtrlConsumed + 16 + r] = ld_acquire_sys(my_pad + kPadGrads + r);
+                    }
+                    if (bad) atomicMax(&s_bad, bad);
+                    s_mask = m;
+                    *reinterpret_cast<volatile uint32_t*>(ctrl + kCtrlMask) = m;
+                    __threadfence();
+                    atomicExch(ctrl + kCtrlGo, seq);
+                }
+            } else if (tid == 0) {
+                while (static_cast<int32_t>(atomicAdd(ctrl + kCtrlGo, 0u) - seq) < 0) {
+                }
+                s_mask = ld_volatile_u32(ctrl + kCtrlMask);
+                __threadfence_system();
+            }
+        }
+        __syncthreads();
+        if (!all_ranks && (a.phases & (PSB_PUSH_WAIT_GRADS | PSB_PUSH_TRY_GRADS))) {
+            mask = s_mask;
+            if (!each && mask != 0) inv = 1.0f / static_cast<float>(__popc(mask));
+        }
+        if (a.prof != nullptr && first_block && tid == 0) a.prof[1] = global_ns();
+    }
+    const int bad_grads = s_bad;
+    const bool go = bad_grads == 0 && mask != 0;
+
+    // ---------------- reduce + apply + cast for this block's share of its segment
+    if (has_work && go) {
         OptCtx o;
         o.kind = s.opt_kind; o.lr = s.lr; o.h1 = s.h1; o.h2 = s.h2; o.eps = s.eps; o.lr_t = s.lr;
         if (s.opt_kind == 2) {
             const float b1p = s.beta_pow[0], b2p = s.beta_pow[1];
             o.lr_t = s.lr * sqrtf(1.0f - b2p) / (1.0f - b1p);
         }
-        float* master = s.master;
-        float* s0 = s.slot0;
-        float* s1 = s.slot1;
+        float* const master = s.master;
+        float* const s0 = s.slot0;
+        float* const s1 = s.slot1;
         const int cols = static_cast<int>(s.cols);
-        const bool vec = (s.numel % 4 == 0) && (s.grad_offset % 4 == 0) && (cols % 4 == 0) &&
-                         ((reinterpret_cast<uintptr_t>(master) & 15) == 0) &&
-                         !(a.async_sgd_atomic && s.opt_kind == 0);
+        const bool aligned = (s.grad_offset % 4 == 0) && ((reinterpret_cast<uintptr_t>(master) & 15) == 0);
+        const bool atomic_sgd = a.async_sgd_atomic && o.kind == 0;
+        const bool need_g = o.kind >= 0;
+        const bool zero_g = (s.flags & PSB_SEG_ZERO_GRAD) != 0 && need_g;
         const int n_dst = s.bcast ? a.n_arenas : 1;
         if (s.w_off >= 0 || s.wt_off >= 0) {
             // ---- matrices: 32x32 tiles so that BOTH bf16 copies are written in full 32-byte
             // sectors (the transposed copy goes through a shared-memory transpose).  Two tiles
-            // per iteration: all loads, then the math, then the stores.
-            __shared__ __nv_bfloat16 tile[2][32][34];
+            // per iteration: every peer load of both tiles first, then the math, then the stores.
             const int rows = static_cast<int>(s.numel / s.cols);
             const int tcols = (cols + 31) >> 5, trows = (rows + 31) >> 5;
             const int ntiles = tcols * trows;
             const int ty = tid >> 3, tx4 = (tid & 7) * 4;
-            const bool atomic_sgd = a.async_sgd_atomic && o.kind == 0;
-            const bool v4 = (cols % 4 == 0) && (s.grad_offset % 4 == 0) && ((reinterpret_cast<uintptr_t>(master) & 15) == 0);
-            for (int t0 = blockIdx.x * 2; t0 < ntiles; t0 += gridDim.x * 2) {
-                float g[2][4], w[2][4], v0[2][4], v1[2][4];
+            const bool v4 = aligned && (cols % 4 == 0);
+            constexpr int TU = MAXW >= 8 ? 1 : 2;      // tiles per iteration (register budget: TU * MAXW peer loads)
+            for (int t0 = blockIdx.x * TU; t0 < ntiles; t0 += nb * TU) {
+                float4 t[TU][MAXW];
+                float4 w[TU], v0[TU], v1[TU];
+                bool live[TU];
+                int nv[TU];
 #pragma unroll
-                for (int u = 0; u < 2; ++u) {
+                for (int u = 0; u < TU; ++u) {
                     const int tI = t0 + u;
                     const int r = (tI / tcols) * 32 + ty, c = (tI % tcols) * 32 + tx4;
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) g[u][e] = w[u][e] = v0[u][e] = v1[u][e] = 0.0f;
-                    if (tI < ntiles && r < rows && c < cols) {
+                    live[u] = tI < ntiles && r < rows && c < cols;
+                    nv[u] = live[u] ? min(4, cols - c) : 0;
+                    w[u] = v0[u] = v1[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (live[u]) {
                         const size_t i = static_cast<size_t>(r) * cols + c;
-                        if (v4) {
-                            // all ranks' slices first (independent NVLink loads in flight together),
-                            // then the sum in rank order (deterministic)
-                            float4 t[8];
+                        if (need_g) {
 #pragma unroll
-                            for (int rk = 0; rk < 8; ++rk)
-                                if (rk < a.world) t[rk] = ld_volatile_v4(a.grad_ptrs[rk] + s.grad_offset + i);
-#pragma unroll
-                            for (int rk = 0; rk < 8; ++rk)
-                                if (rk < a.world) { g[u][0] += t[rk].x; g[u][1] += t[rk].y; g[u][2] += t[rk].z; g[u][3] += t[rk].w; }
-                            for (int rk = 8; rk < a.world; ++rk) {
-                                const float4 tt = ld_volatile_v4(a.grad_ptrs[rk] + s.grad_offset + i);
-                                g[u][0] += tt.x; g[u][1] += tt.y; g[u][2] += tt.z; g[u][3] += tt.w;
-                            }
-                            if (!atomic_sgd) {
-                                const float4 t = *reinterpret_cast<const float4*>(master + i);
-                                w[u][0] = t.x; w[u][1] = t.y; w[u][2] = t.z; w[u][3] = t.w;
-                            }
-                            if (o.kind > 0) {
-                                const float4 p0 = *reinterpret_cast<const float4*>(s0 + i);
-                                const float4 p1 = *reinterpret_cast<const float4*>(s1 + i);
-                                v0[u][0] = p0.x; v0[u][1] = p0.y; v0[u][2] = p0.z; v0[u][3] = p0.w;
-                                v1[u][0] = p1.x; v1[u][1] = p1.y; v1[u][2] = p1.z; v1[u][3] = p1.w;
-                            }
-                        } else {
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                if (c + e < cols) {
-                                    for (int rk = 0; rk < a.world; ++rk) g[u][e] += ld_volatile_f32(a.grad_ptrs[rk] + s.grad_offset + i + e);
-                                    if (!atomic_sgd) w[u][e] = master[i + e];
-                                    if (o.kind > 0) { v0[u][e] = s0[i + e]; v1[u][e] = s1[i + e]; }
-                                }
-                            }
+                            for (int rk = 0; rk < MAXW; ++rk)
+                                if (rk < a.world && ((mask >> rk) & 1u)) t[u][rk] = ld4_cg(s_grad[rk] + s.grad_offset + i, v4, nv[u]);
                         }
+                        if (!atomic_sgd) w[u] = ld4(master + i, v4, nv[u]);
+                        if (o.kind > 0) { v0[u] = ld4(s0 + i, v4, nv[u]); v1[u] = ld4(s1 + i, v4, nv[u]); }
                     }
                 }
 #pragma unroll
-                for (int u = 0; u < 2; ++u) {
+                for (int u = 0; u < TU; ++u) {
                     const int tI = t0 + u;
                     const int r = (tI / tcols) * 32 + ty, c = (tI % tcols) * 32 + tx4;
-                    const bool live = tI < ntiles && r < rows && c < cols;
-                    if (live) {
+                    float wv[4] = {0.f, 0.f, 0.f, 0.f};
+                    if (live[u]) {
                         const size_t i = static_cast<size_t>(r) * cols + c;
+                        if (atomic_sgd) {
+                            float gs[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float gg = g[u][e] * a.inv_replicas;
-                            if (c + e < cols) {
-                                if (atomic_sgd) w[u][e] = atomicAdd(master + i + e, -o.lr * gg) - o.lr * gg;
-                                else w[u][e] = apply_val(o, w[u][e], gg, v0[u][e], v1[u][e]);
-                            }
-                        }
-                        if (v4) {
-                            if (!atomic_sgd) *reinterpret_cast<float4*>(master + i) = make_float4(w[u][0], w[u][1], w[u][2], w[u][3]);
-                            if (o.kind > 0) {
-                                *reinterpret_cast<float4*>(s0 + i) = make_float4(v0[u][0], v0[u][1], v0[u][2], v0[u][3]);
-                                *reinterpret_cast<float4*>(s1 + i) = make_float4(v1[u][0], v1[u][1], v1[u][2], v1[u][3]);
-                            }
-                        } else {
+                            for (int rk = 0; rk < MAXW; ++rk)
+                                if (rk < a.world && ((mask >> rk) & 1u)) { gs[0] += t[u][rk].x; gs[1] += t[u][rk].y; gs[2] += t[u][rk].z; gs[3] += t[u][rk].w; }
 #pragma unroll
                             for (int e = 0; e < 4; ++e) {
-                                if (c + e < cols) {
-                                    if (!atomic_sgd) master[i + e] = w[u][e];
-                                    if (o.kind > 0) { s0[i + e] = v0[u][e]; s1[i + e] = v1[u][e]; }
+                                if (e < nv[u]) {
+                                    const float d = -o.lr * gs[e] * inv;
+                                    wv[e] = atomicAdd(master + i + e, d) + d;
                                 }
                             }
+                        } else {
+                            if (need_g) apply4(o, t[u], a.world, mask, each, inv, w[u], v0[u], v1[u]);
+                            st4(master + i, w[u], v4, nv[u]);
+                            if (o.kind > 0) { st4(s0 + i, v0[u], v4, nv[u]); st4(s1 + i, v1[u], v4, nv[u]); }
+                            wv[0] = w[u].x; wv[1] = w[u].y; wv[2] = w[u].z; wv[3] = w[u].w;
+                        }
+                        if (zero_g) {
+                            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                            for (int rk = 0; rk < a.world; ++rk)
+                                st4(const_cast<float*>(s_grad[rk]) + s.grad_offset + i, z, v4, nv[u]);
                         }
                     }
 #pragma unroll
-                    for (int e = 0; e < 4; ++e) tile[u][ty][tx4 + e] = __float2bfloat16_rn(live && c + e < cols ? w[u][e] : 0.0f);
-                    if (live && s.w_off >= 0) {
-                        const uint32_t lo = pack_bf16(w[u][0], w[u][1]), hi = pack_bf16(w[u][2], w[u][3]);
+                    for (int e = 0; e < 4; ++e) tile[u][ty][tx4 + e] = __float2bfloat16_rn(e < nv[u] ? wv[e] : 0.0f);
+                    if (live[u] && s.w_off >= 0) {
+                        const uint32_t lo = pack_bf16(wv[0], wv[1]), hi = pack_bf16(wv[2], wv[3]);
                         for (int d = 0; d < n_dst; ++d) {
-                            __nv_bfloat16* p = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]) + s.w_off +
-                                               static_cast<size_t>(r) * s.ld_w + c;
-                            if (c + 3 < cols) {
+                            __nv_bfloat16* p = s_arena[s.bcast ? d : s.home] + s.w_off + static_cast<size_t>(r) * s.ld_w + c;
+                            if (nv[u] == 4) {
                                 *reinterpret_cast<uint2*>(p) = make_uint2(lo, hi);
                             } else {
-                                for (int e = 0; e < 4 && c + e < cols; ++e) p[e] = __float2bfloat16_rn(w[u][e]);
+#pragma unroll
+                                for (int e = 0; e < 4; ++e)
+                                    if (e < nv[u]) p[e] = __float2bfloat16_rn(wv[e]);
                             }
                         }
                     }
@@ -252,7 +422,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                 __syncthreads();
                 if (s.wt_off >= 0) {
 #pragma unroll
-                    for (int u = 0; u < 2; ++u) {
+                    for (int u = 0; u < TU; ++u) {
                         const int tI = t0 + u;
                         // thread (cc = ty, rr4 = tx4): column cc of the tile, rows rr4..rr4+3 -> 8 contiguous bytes of wt
                         const int cg = (tI % tcols) * 32 + ty, rg = (tI / tcols) * 32 + tx4;
@@ -260,8 +430,7 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                             const __nv_bfloat16 b0 = tile[u][tx4][ty], b1 = tile[u][tx4 + 1][ty], b2 = tile[u][tx4 + 2][ty],
                                                 b3 = tile[u][tx4 + 3][ty];
                             for (int d = 0; d < n_dst; ++d) {
-                                __nv_bfloat16* p = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]) + s.wt_off +
-                                                   static_cast<size_t>(cg) * s.ld_wt + rg;
+                                __nv_bfloat16* p = s_arena[s.bcast ? d : s.home] + s.wt_off + static_cast<size_t>(cg) * s.ld_wt + rg;
                                 if (rg + 3 < rows) {
                                     uint2 pk;
                                     pk.x = static_cast<uint32_t>(__bfloat16_as_ushort(b0)) | (static_cast<uint32_t>(__bfloat16_as_ushort(b1)) << 16);
@@ -279,146 +448,119 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
                 __syncthreads();
             }
         } else {
-        constexpr int U = 4;      // independent vectors per thread per iteration: all loads, then math, then stores
-        if (vec) {
-            const uint32_t n4 = s.numel / 4;
-            for (uint32_t base = blockIdx.x * (kPushThreads * U); base < n4; base += gridDim.x * (kPushThreads * U)) {
-                float4 g[U], w[U], v0[U], v1[U];
+            // ---- vectors (biases, flat shards): groups of four, U groups per thread per iteration
+            constexpr int U = MAXW >= 8 ? 1 : (MAXW >= 4 ? 2 : 4);   // >= 4 (8 from MAXW = 2) 128-bit loads in flight per thread
+            const uint32_t n4 = (s.numel + 3) / 4;
+            for (uint32_t base = blockIdx.x * (kPushThreads * U); base < n4; base += nb * (kPushThreads * U)) {
+                float4 t[U][MAXW];
+                float4 w[U], v0[U], v1[U];
+                int nv[U];
 #pragma unroll
                 for (int j = 0; j < U; ++j) {
                     const uint32_t i4 = base + j * kPushThreads + tid;
-                    g[j] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    w[j] = v0[j] = v1[j] = g[j];
-                    if (i4 < n4) {
+                    nv[j] = i4 < n4 ? min(4u, s.numel - i4 * 4) : 0;
+                    w[j] = v0[j] = v1[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (nv[j] > 0) {
                         const size_t i = static_cast<size_t>(i4) * 4;
-                        float4 t[8];
+                        const bool v4 = aligned && nv[j] == 4;
+                        if (need_g) {
 #pragma unroll
-                        for (int r = 0; r < 8; ++r)
-                            if (r < a.world) t[r] = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
-#pragma unroll
-                        for (int r = 0; r < 8; ++r)
-                            if (r < a.world) { g[j].x += t[r].x; g[j].y += t[r].y; g[j].z += t[r].z; g[j].w += t[r].w; }
-                        for (int r = 8; r < a.world; ++r) {
-                            const float4 tt = ld_volatile_v4(a.grad_ptrs[r] + s.grad_offset + i);
-                            g[j].x += tt.x; g[j].y += tt.y; g[j].z += tt.z; g[j].w += tt.w;
+                            for (int rk = 0; rk < MAXW; ++rk)
+                                if (rk < a.world && ((mask >> rk) & 1u)) t[j][rk] = ld4_cg(s_grad[rk] + s.grad_offset + i, v4, nv[j]);
                         }
-                        w[j] = *reinterpret_cast<const float4*>(master + i);
-                        if (o.kind > 0) {
-                            v0[j] = *reinterpret_cast<const float4*>(s0 + i);
-                            v1[j] = *reinterpret_cast<const float4*>(s1 + i);
-                        }
+                        if (!atomic_sgd) w[j] = ld4(master + i, v4, nv[j]);
+                        if (o.kind > 0) { v0[j] = ld4(s0 + i, v4, nv[j]); v1[j] = ld4(s1 + i, v4, nv[j]); }
                     }
                 }
 #pragma unroll
                 for (int j = 0; j < U; ++j) {
+                    if (nv[j] == 0) continue;
                     const uint32_t i4 = base + j * kPushThreads + tid;
-                    if (i4 >= n4) continue;
                     const size_t i = static_cast<size_t>(i4) * 4;
-                    const float sc = a.inv_replicas;
-                    w[j].x = apply_val(o, w[j].x, g[j].x * sc, v0[j].x, v1[j].x);
-                    w[j].y = apply_val(o, w[j].y, g[j].y * sc, v0[j].y, v1[j].y);
-                    w[j].z = apply_val(o, w[j].z, g[j].z * sc, v0[j].z, v1[j].z);
-                    w[j].w = apply_val(o, w[j].w, g[j].w * sc, v0[j].w, v1[j].w);
-                    *reinterpret_cast<float4*>(master + i) = w[j];
-                    if (o.kind > 0) {
-                        *reinterpret_cast<float4*>(s0 + i) = v0[j];
-                        *reinterpret_cast<float4*>(s1 + i) = v1[j];
-                    }
-                    const int row = static_cast<int>(i / cols), col = static_cast<int>(i % cols);
-                    const __nv_bfloat162 lo = __floats2bfloat162_rn(w[j].x, w[j].y), hi = __floats2bfloat162_rn(w[j].z, w[j].w);
-                    for (int d = 0; d < n_dst; ++d) {
-                        __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
-                        if (s.w_off >= 0) {
-                            __nv_bfloat16* p = arena + s.w_off + static_cast<size_t>(row) * s.ld_w + col;
-                            uint2 pk;
-                            pk.x = *reinterpret_cast<const uint32_t*>(&lo);
-                            pk.y = *reinterpret_cast<const uint32_t*>(&hi);
-                            *reinterpret_cast<uint2*>(p) = pk;
-                        }
-                        if (s.f_off >= 0)
-                            *reinterpret_cast<float4*>(a.farena_ptrs[s.bcast ? d : s.home] + s.f_off + i) = w[j];
-                        if (s.wt_off >= 0) {
-                            __nv_bfloat16* p = arena + s.wt_off + static_cast<size_t>(col) * s.ld_wt + row;
-                            p[0] = lo.x;
-                            p[s.ld_wt] = lo.y;
-                            p[2 * static_cast<size_t>(s.ld_wt)] = hi.x;
-                            p[3 * static_cast<size_t>(s.ld_wt)] = hi.y;
-                        }
-                    }
-                }
-            }
-        } else {
-            constexpr int US = 8;
-            for (uint32_t base = blockIdx.x * (kPushThreads * US); base < s.numel; base += gridDim.x * (kPushThreads * US)) {
-                float g[US], w[US], v0[US], v1[US];
-                const bool atomic_sgd = a.async_sgd_atomic && o.kind == 0;
-#pragma unroll
-                for (int j = 0; j < US; ++j) {
-                    const uint32_t i = base + j * kPushThreads + tid;
-                    g[j] = w[j] = v0[j] = v1[j] = 0.0f;
-                    if (i < s.numel) {
-                        for (int r = 0; r < a.world; ++r) g[j] += ld_volatile_f32(a.grad_ptrs[r] + s.grad_offset + i);
-                        if (!atomic_sgd) w[j] = master[i];
-                        if (o.kind > 0) { v0[j] = s0[i]; v1[j] = s1[i]; }
-                    }
-                }
-#pragma unroll
-                for (int j = 0; j < US; ++j) {
-                    const uint32_t i = base + j * kPushThreads + tid;
-                    if (i >= s.numel) continue;
-                    const float gg = g[j] * a.inv_replicas;
-                    float wn;
+                    const bool v4 = aligned && nv[j] == 4;
                     if (atomic_sgd) {
-                        wn = atomicAdd(master + i, -o.lr * gg) - o.lr * gg;
+                        float gs[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                        for (int rk = 0; rk < MAXW; ++rk)
+                            if (rk < a.world && ((mask >> rk) & 1u)) { gs[0] += t[j][rk].x; gs[1] += t[j][rk].y; gs[2] += t[j][rk].z; gs[3] += t[j][rk].w; }
+                        float wv[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            if (e < nv[j]) {
+                                const float d = -o.lr * gs[e] * inv;
+                                wv[e] = atomicAdd(master + i + e, d) + d;
+                            }
+                        }
+                        w[j] = make_float4(wv[0], wv[1], wv[2], wv[3]);
                     } else {
-                        wn = apply_val(o, w[j], gg, v0[j], v1[j]);
-                        master[i] = wn;
-                        if (o.kind > 0) { s0[i] = v0[j]; s1[i] = v1[j]; }
+                        if (need_g) apply4(o, t[j], a.world, mask, each, inv, w[j], v0[j], v1[j]);
+                        st4(master + i, w[j], v4, nv[j]);
+                        if (o.kind > 0) { st4(s0 + i, v0[j], v4, nv[j]); st4(s1 + i, v1[j], v4, nv[j]); }
                     }
-                    const int row = static_cast<int>(i / cols), col = static_cast<int>(i % cols);
-                    const __nv_bfloat16 wb = __float2bfloat16_rn(wn);
-                    for (int d = 0; d < n_dst; ++d) {
-                        __nv_bfloat16* arena = static_cast<__nv_bfloat16*>(a.arena_ptrs[s.bcast ? d : s.home]);
-                        if (s.w_off >= 0) arena[s.w_off + static_cast<size_t>(row) * s.ld_w + col] = wb;
-                        if (s.f_off >= 0) a.farena_ptrs[s.bcast ? d : s.home][s.f_off + i] = wn;
-                        if (s.wt_off >= 0) arena[s.wt_off + static_cast<size_t>(col) * s.ld_wt + row] = wb;
+                    if (zero_g) {
+                        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int rk = 0; rk < a.world; ++rk)
+                            st4(const_cast<float*>(s_grad[rk]) + s.grad_offset + i, z, v4, nv[j]);
+                    }
+                    if (s.f_off >= 0) {
+                        // the fp32 arena is padded to whole groups of four: full 128-bit stores
+                        const bool fv4 = ((s.f_off + i) % 4 == 0);
+                        for (int d = 0; d < n_dst; ++d)
+                            st4(s_farena[s.bcast ? d : s.home] + s.f_off + i, w[j], fv4 && nv[j] == 4, nv[j]);
                     }
                 }
             }
-        }
         }
     }
 
     // ---------------- completion: last block finishes the step
     __syncthreads();
-    __shared__ bool is_last;
     if (tid == 0) {
+        if (bad_grads) atomicMax(ctrl + kCtrlStatus, static_cast<uint32_t>(bad_grads));
         __threadfence_system();
-        const uint32_t prev = atomicAdd(a.local_ctrl + 1, 1u);
+        const uint32_t prev = atomicAdd(ctrl + kCtrlDone, 1u);
         is_last = (prev == total_blocks - 1);
     }
     __syncthreads();
     unsigned long long t_applied = 0;
     if (is_last) {
+        const bool failed = ld_volatile_u32(ctrl + kCtrlStatus) != 0;
+        const bool applied = go && !failed && (a.phases & PSB_PUSH_APPLY);
         if (tid == 0) {
             if (a.prof != nullptr) t_applied = global_ns();
-            a.local_ctrl[1] = 0;
-            if (auto_step) a.local_ctrl[2] = a.step_id;
-            for (int k = 0; k < a.nbeta; ++k) {
-                a.beta[k].beta_pow[0] *= a.beta[k].beta1;
-                a.beta[k].beta_pow[1] *= a.beta[k].beta2;
+            ctrl[kCtrlDone] = 0;
+            ctrl[kCtrlSeq] = seq;
+            if (applied) {
+                const int napplied = each ? __popc(mask) : 1;
+                if (auto_step) ctrl[kCtrlStep] = a.step_id;
+                ctrl[kCtrlApplied] += napplied;
+                for (int k = 0; k < a.nbeta; ++k) {
+                    for (int n = 0; n < napplied; ++n) {
+                        a.beta[k].beta_pow[0] *= a.beta[k].beta1;
+                        a.beta[k].beta_pow[1] *= a.beta[k].beta2;
+                    }
+                }
+                if (a.global_step != nullptr && a.step_delta != 0) atomicAdd(a.global_step, a.step_delta * napplied);
+                if (each)
+                    for (int r = 0; r < a.world; ++r)
+                        if ((mask >> r) & 1u) ctrl[kCtrlConsumed + r] = ctrl[kCtrlConsumed + 16 + r];
             }
-            if (a.global_step != nullptr && a.step_delta != 0) atomicAdd(a.global_step, a.step_delta);
             __threadfence_system();
         }
         __syncthreads();
-        if (a.world > 1 && a.signal_params && tid < a.world) {
-            st_release_sys(a.pad_ptrs[tid] + kPadParams + a.rank, a.step_id);
+        if (a.world > 1 && applied && tid < a.world) {
+            if (each) {
+                // tell every sender whose gradient was consumed that its buffer is free again
+                if ((mask >> tid) & 1u) st_release_sys(a.pad_ptrs[tid] + kPadAck + a.rank, ctrl[kCtrlConsumed + tid]);
+            } else if (a.phases & PSB_PUSH_SIGNAL_PARAMS) {
+                st_release_sys(a.pad_ptrs[tid] + kPadParams + a.rank, a.step_id);
+            }
+        }
+        if (a.world > 1 && !failed && (a.phases & PSB_PUSH_WAIT_PARAMS) && tid < a.world) {
             // ...and do not let this stream run ahead until every owner has finished writing
             // this step's parameters (they may be writing into OUR arena).
-            const uint32_t* mine = a.pad_ptrs[a.rank] + kPadParams + tid;
-            while (static_cast<int32_t>(ld_acquire_sys(mine) - a.step_id) < 0) {
-            }
+            const int bad = spin_flag(my_pad + kPadParams + tid, a.step_id, sp, PSB_PUSH_ST_TIMEOUT_PARAMS);
+            if (bad) atomicMax(ctrl + kCtrlStatus, static_cast<uint32_t>(bad));
         }
         if (a.prof != nullptr) {
             __syncthreads();
@@ -435,6 +577,64 @@ __global__ void __launch_bounds__(kPushThreads) push_apply_kernel(PushArgs a) {
     }
 }
 
+// Worker half of the decoupled protocol (the ps half is push_apply_kernel launched by the ps
+// service).  One block.
+//   sync  : publish "my gradients for token s are complete", wait until every owner has applied
+//           aggregate >= s, adopt min(applied) + 1 as the next token (a late worker skips ahead:
+//           its gradient was stale and has been dropped)
+//   async : publish "my gradient number n is complete" (wait = 0), or wait until every owner has
+//           acknowledged gradient number ctrl[2] (wait = 1; issued before the next backward pass
+//           overwrites the gradient buffer)
+struct CommitArgs {
+    uint32_t* const* pad_ptrs;
+    int world, rank;
+    uint32_t* ctrl;          // worker control words: [2] token / gradient number, [3] status, [4] abort
+    int async_mode;
+    int wait;
+    unsigned long long timeout_ns;
+};
+
+__global__ void push_commit_kernel(CommitArgs a) {
+    const int tid = threadIdx.x;
+    __shared__ uint32_t s_min[kMaxWorld];
+    const Spin sp{a.ctrl + kCtrlAbort, a.timeout_ns};
+    uint32_t* my_pad = a.pad_ptrs[a.rank];
+    if (a.async_mode) {
+        if (a.wait) {
+            const uint32_t n = ld_volatile_u32(a.ctrl + kCtrlStep);
+            if (tid < a.world && n != 0) {
+                const int bad = spin_flag(my_pad + kPadAck + tid, n, sp, PSB_PUSH_ST_TIMEOUT_PARAMS);
+                if (bad) atomicMax(a.ctrl + kCtrlStatus, static_cast<uint32_t>(bad));
+            }
+        } else {
+            const uint32_t n = ld_volatile_u32(a.ctrl + kCtrlStep) + 1;
+            if (tid < a.world) {
+                __threadfence_system();
+                st_release_sys(a.pad_ptrs[tid] + kPadGrads + a.rank, n);
+            }
+            __syncthreads();
+            if (tid == 0) a.ctrl[kCtrlStep] = n;
+        }
+        return;
+    }
+    uint32_t token = ld_volatile_u32(a.ctrl + kCtrlStep);
+    if (token == 0) token = 1;
+    if (tid < a.world) {
+        __threadfence_system();
+        st_release_sys(a.pad_ptrs[tid] + kPadGrads + a.rank, token);
+        const int bad = spin_flag(my_pad + kPadParams + tid, token, sp, PSB_PUSH_ST_TIMEOUT_PARAMS);
+        if (bad) atomicMax(a.ctrl + kCtrlStatus, static_cast<uint32_t>(bad));
+        s_min[tid] = ld_acquire_sys(my_pad + kPadParams + tid);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t m = s_min[0];
+        for (int r = 1; r < a.world; ++r)
+            if (static_cast<int32_t>(s_min[r] - m) < 0) m = s_min[r];
+        a.ctrl[kCtrlStep] = m + 1;
+    }
+}
+
 // Spin until every rank has published params-ready >= step_id (used by consumers that read
 // peers' arenas directly and by tests).
 __global__ void wait_params_kernel(uint32_t* pad, int world, uint32_t step_id) {
@@ -444,33 +644,92 @@ __global__ void wait_params_kernel(uint32_t* pad, int world, uint32_t step_id) {
     }
 }
 
+static int check_desc(const psb_push_desc_t* d, const char* who, bool device_tables) {
+    if (!d) return fail(PSB_ERR_ARG, "%s: null descriptor", who);
+    if (d->world < 1 || d->world > kMaxWorld || d->rank < 0 || d->rank >= d->world)
+        return fail(PSB_ERR_ARG, "%s: world must be 1..16 and 0 <= rank < world", who);
+    if (d->nbeta < 0 || d->nbeta > 2) return fail(PSB_ERR_ARG, "%s: at most two Adam optimizers", who);
+    if (device_tables) {
+        if (d->nseg < 0 || (d->nseg > 0 && !d->segs)) return fail(PSB_ERR_ARG, "%s: bad segment table", who);
+        if (!d->grad_ptrs || !d->arena_ptrs || !d->farena_ptrs || !d->local_ctrl) return fail(PSB_ERR_ARG, "%s: null table", who);
+        if (d->world > 1 && !d->pad_ptrs) return fail(PSB_ERR_ARG, "%s: world > 1 needs signal pads", who);
+    }
+    if ((d->phases & PSB_PUSH_EACH) && d->async_sgd_atomic)
+        return fail(PSB_ERR_ARG, "%s: PSB_PUSH_EACH applies on the owner; it excludes async_sgd_atomic", who);
+    return PSB_OK;
+}
+
+static void fill_args(PushArgs& a, const psb_push_desc_t* d) {
+    a.world = d->world; a.rank = d->rank; a.n_arenas = d->n_arenas > 0 ? d->n_arenas : d->world;
+    a.inv_replicas = d->inv_replicas;
+    a.step_id = d->step_id;
+    a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
+    a.global_step = d->global_step; a.step_delta = d->step_delta;
+    a.async_sgd_atomic = d->async_sgd_atomic;
+    a.phases = d->phases;
+    if (a.phases == 0) {
+        a.phases = PSB_PUSH_APPLY;
+        if (d->world > 1) {
+            a.phases |= PSB_PUSH_SIGNAL_GRADS | PSB_PUSH_WAIT_GRADS;
+            if (d->signal_params) a.phases |= PSB_PUSH_SIGNAL_PARAMS | PSB_PUSH_WAIT_PARAMS;
+        }
+    }
+    a.replicas = d->replicas;
+    a.prof = reinterpret_cast<unsigned long long*>(d->prof);
+    a.timeout_ns = d->timeout_ns;
+}
+
+static int launch_push(const PushArgs& a, dim3 grid, cudaStream_t st, bool pdl) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kPushThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    cudaError_t e;
+    if (a.world <= 1) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<1>, a);
+    else if (a.world <= 2) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<2>, a);
+    else if (a.world <= 4) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<4>, a);
+    else if (a.world <= 8) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<8>, a);
+    else e = cudaLaunchKernelEx(&cfg, push_apply_kernel<16>, a);
+    if (e != cudaSuccess) return fail(PSB_ERR_CUDA, "push_apply launch failed: %s", cudaGetErrorString(e));
+    return PSB_OK;
+}
+
 }  // namespace psb
 
 extern "C" int psb_push_apply(const psb_push_desc_t* d, void* stream) {
     using namespace psb;
-    if (!d) return fail(PSB_ERR_ARG, "psb_push_apply: null descriptor");
-    if (d->world < 1 || d->world > 16 || d->rank < 0 || d->rank >= d->world)
-        return fail(PSB_ERR_ARG, "psb_push_apply: world must be 1..16 and 0 <= rank < world");
-    if (d->nseg < 0 || (d->nseg > 0 && !d->segs)) return fail(PSB_ERR_ARG, "psb_push_apply: bad segment table");
-    if (!d->grad_ptrs || !d->arena_ptrs || !d->farena_ptrs || !d->local_ctrl) return fail(PSB_ERR_ARG, "psb_push_apply: null table");
-    if (d->world > 1 && !d->pad_ptrs) return fail(PSB_ERR_ARG, "psb_push_apply: world > 1 needs signal pads");
-    if (d->nbeta < 0 || d->nbeta > 2) return fail(PSB_ERR_ARG, "psb_push_apply: at most two Adam optimizers");
+    int rc = check_desc(d, "psb_push_apply", true);
+    if (rc != PSB_OK) return rc;
     PushArgs a;
     a.segs = d->segs; a.nseg = d->nseg; a.grad_ptrs = d->grad_ptrs; a.arena_ptrs = d->arena_ptrs;
-    a.farena_ptrs = d->farena_ptrs; a.pad_ptrs = d->pad_ptrs; a.world = d->world; a.rank = d->rank; a.n_arenas = d->n_arenas > 0 ? d->n_arenas : d->world; a.inv_replicas = d->inv_replicas;
-    a.step_id = d->step_id; a.local_ctrl = d->local_ctrl;
-    a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
-    a.global_step = d->global_step; a.step_delta = d->step_delta;
-    a.async_sgd_atomic = d->async_sgd_atomic; a.signal_params = d->signal_params;
-    a.prof = reinterpret_cast<unsigned long long*>(d->prof);
+    a.farena_ptrs = d->farena_ptrs; a.pad_ptrs = d->pad_ptrs; a.local_ctrl = d->local_ctrl;
+    fill_args(a, d);
     int gx = d->blocks_per_seg > 0 ? d->blocks_per_seg : 16;
-    if (gx > 296) gx = 296;
+    if (gx > 592) gx = 592;
     dim3 grid(gx, d->nseg > 0 ? d->nseg : 1);
-    // the blocks spin on each other: all of them must be resident (2 x 256 threads per SM fit easily)
-    if (d->world > 1 && grid.x * grid.y > 296)
+    // blocks of one launch wait for each other's decision (R of N) and for peers: all of them must be
+    // resident (4 x 256 threads per SM fit in registers and shared memory)
+    if (d->world > 1 && grid.x * grid.y > 592)
         return fail(PSB_ERR_LIMIT, "psb_push_apply: grid %u x %u would not be co-resident", grid.x, grid.y);
-    push_apply_kernel<<<grid, kPushThreads, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    rc = launch_push(a, grid, static_cast<cudaStream_t>(stream), true);
+    if (rc != PSB_OK) return rc;
     return after_launch("push_apply");
+}
+
+extern "C" int psb_push_commit(uint32_t* const* pad_ptrs, int world, int rank, uint32_t* worker_ctrl,
+                               int async_mode, int wait, uint64_t timeout_ns, void* stream) {
+    using namespace psb;
+    if (!pad_ptrs || !worker_ctrl || world < 1 || world > kMaxWorld || rank < 0 || rank >= world)
+        return fail(PSB_ERR_ARG, "psb_push_commit: bad argument");
+    CommitArgs a{pad_ptrs, world, rank, worker_ctrl, async_mode, wait, timeout_ns};
+    push_commit_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(a);
+    return after_launch("push_commit");
 }
 
 extern "C" int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream) {
@@ -481,45 +740,52 @@ extern "C" int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void*
 }
 
 // ======================================================================================
-// psb_push_apply_noalloc — the same kernel for callers that are not allowed to allocate.
+// psb_push_apply_noalloc -- the same kernel for callers that are not allowed to allocate.
 //
 // psb_push_apply needs three kinds of device memory besides the tensors it works on: the
-// control words the kernel uses as scratch (go flag, finished-block counter, step token),
+// control words the kernel uses as scratch (finished-block counter, step token, status),
 // the segment table and the per-rank pointer tables.  Somebody has to cudaMalloc those.
 // Some callers cannot: an optimizer hook that runs inside another framework's memory pool
 // and must not touch the CUDA allocator, a plug-in whose host forbids allocations after
 // start-up, or code on a latency path where an allocation (an implicit device
 // synchronisation) is not acceptable.  For them this entry point keeps all of that in ONE
 // file-scope device array of fixed size, so the library's own image provides the memory:
-// every GPU that loads this library holds sizeof(NoAllocScratch) bytes (about 7 KiB) until
-// the process exits, whether or not this entry point is ever called.
+// every GPU that loads this library holds sizeof(NoAllocScratch) = 8960 bytes (8.75 KiB)
+// until the process exits, whether or not this entry point is ever called.
 //
 // What the caller must know
 //   * Limits: at most PSB_NOALLOC_MAX_SEGS (64) segments and PSB_NOALLOC_MAX_WORLD (16)
-//     ranks/arenas; larger requests are refused with PSB_ERR_LIMIT and a message.
+//     ranks/arenas; larger requests are refused with PSB_ERR_LIMIT and a message.  The grid
+//     is blocks_per_seg (default 16, at most 64) x nseg for every nseg up to the limit.
 //   * The segment table and the pointer tables are passed as HOST arrays and copied into the
-//     scratch with cudaMemcpyAsync on `stream` before the launch.  Pageable arrays may be
-//     reused as soon as the call returns; pinned arrays must stay unchanged until the stream
-//     has passed the copies.
+//     scratch with cudaMemcpyAsync on `stream` before the launch: keep them valid and
+//     unchanged until the stream has passed those copies.
 //   * The first call on each device looks up the device address of the array
 //     (cudaGetSymbolAddress, with that device current) and caches it.  Make that first call
 //     outside any stream capture.
 //   * All calls on a device share the one array and it keeps what the previous call left
-//     there.  The finished-block counter is cleared on every call; the go flag and the step
-//     token are deliberately kept, because the multi-GPU handshake compares against them.
-//     Two calls that overlap on the GPU (different streams, or graphs replayed concurrently)
+//     there.  The finished-block counter is cleared on every call; the step token, the
+//     launch sequence number and the status word are deliberately kept, because the
+//     multi-GPU handshake compares against the token.  So, per device and for the life of
+//     the process: explicit step ids (desc->step_id != 0) must keep increasing across ALL
+//     callers of this entry point, and a caller must not alternate between this entry point
+//     and psb_push_apply (whose token lives in the caller's own local_ctrl) on the same
+//     signal pads -- the two tokens would drift apart and the ranks would wait for
+//     different steps.
+//   * Two calls that overlap on the GPU (different streams, or graphs replayed concurrently)
 //     race on the array: serialise them.
 //   * Nothing here calls cudaMalloc, cudaFree or any allocating library routine.
 namespace psb {
 
 struct NoAllocScratch {
-    uint32_t ctrl[64];                                  // [0] go flag [1] finished blocks [2] step token
+    uint32_t ctrl[PSB_PUSH_CTRL_WORDS];
     psb_push_seg_t segs[PSB_NOALLOC_MAX_SEGS];
     const float* grad_ptrs[PSB_NOALLOC_MAX_WORLD];
     void* arena_ptrs[PSB_NOALLOC_MAX_WORLD];
     float* farena_ptrs[PSB_NOALLOC_MAX_WORLD];
     uint32_t* pad_ptrs[PSB_NOALLOC_MAX_WORLD];
 };
+static_assert(sizeof(NoAllocScratch) == 8960, "update the size quoted in psb200.h, DESIGN.md and INTEGRATION.md");
 
 // In host code this name is only a handle for cudaGetSymbolAddress; the device address it
 // resolves to is what gets passed to the kernel.
@@ -566,15 +832,14 @@ extern "C" int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
     if (!host_grad_ptrs || !host_arena_ptrs || !host_farena_ptrs)
         return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: null pointer table");
     if (d->world > 1 && !host_pad_ptrs) return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: world > 1 needs signal pads");
-    if (d->nbeta < 0 || d->nbeta > 2) return fail(PSB_ERR_ARG, "psb_push_apply_noalloc: at most two Adam optimizers");
+    int rc = check_desc(d, "psb_push_apply_noalloc", false);
+    if (rc != PSB_OK) return rc;
     int gx = d->blocks_per_seg > 0 ? d->blocks_per_seg : 16;
     if (gx > 64) gx = 64;
     dim3 grid(gx, nseg > 0 ? nseg : 1);
-    if (grid.x * grid.y > 148)
-        return fail(PSB_ERR_LIMIT, "psb_push_apply_noalloc: grid %u x %u would not be co-resident", grid.x, grid.y);
 
     NoAllocScratch* sc = nullptr;
-    int rc = noalloc_scratch_for_current_device(&sc);
+    rc = noalloc_scratch_for_current_device(&sc);
     if (rc != PSB_OK) return rc;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     // stage the tables; clear only what must start at zero (the finished-block counter)
@@ -588,13 +853,11 @@ extern "C" int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
 
     PushArgs a;
     a.segs = sc->segs; a.nseg = nseg; a.grad_ptrs = sc->grad_ptrs; a.arena_ptrs = sc->arena_ptrs;
-    a.farena_ptrs = sc->farena_ptrs; a.pad_ptrs = sc->pad_ptrs; a.world = d->world; a.rank = d->rank;
-    a.n_arenas = n_arenas; a.inv_replicas = d->inv_replicas;
-    a.step_id = d->step_id; a.local_ctrl = sc->ctrl;
-    a.beta[0] = d->beta[0]; a.beta[1] = d->beta[1]; a.nbeta = d->nbeta;
-    a.global_step = d->global_step; a.step_delta = d->step_delta;
-    a.async_sgd_atomic = d->async_sgd_atomic; a.signal_params = d->signal_params;
-    a.prof = reinterpret_cast<unsigned long long*>(d->prof);
-    push_apply_kernel<<<grid, kPushThreads, 0, st>>>(a);
+    a.farena_ptrs = sc->farena_ptrs; a.pad_ptrs = sc->pad_ptrs; a.local_ctrl = sc->ctrl;
+    fill_args(a, d);
+    a.n_arenas = n_arenas;
+    // the launch follows copies, not a kernel: no programmatic dependent launch here
+    rc = launch_push(a, grid, st, false);
+    if (rc != PSB_OK) return rc;
     return after_launch("push_apply_noalloc");
 }

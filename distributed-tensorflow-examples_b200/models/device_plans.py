@@ -87,10 +87,12 @@ class EncoderPlan(DevicePlan):
         self.losses["loss"] = torch.zeros((), device=dev)
         self.wkeys = [w for w, _ in enc_mod.LAYERS]
         self.bkeys = [b for _, b in enc_mod.LAYERS]
+        # the bias gradients are accumulated (column sums): the push kernel clears them after use
+        store.zero_after_push([self._name(b) for b in self.bkeys])
 
-    def forward(self, need_t: bool = True) -> None:
+    def forward(self, need_t: bool = True, clear: Optional[torch.Tensor] = None) -> None:
         s, n = self.store, self._name
-        K.cast_transpose(self.inputs["x"], self.act[0], self.act_t[0] if need_t else None)
+        K.cast_transpose(self.inputs["x"], self.act[0], self.act_t[0] if need_t else None, clear=clear)
         for l in range(3):
             K.gemm(self.act[l], s.wt_src(n(self.wkeys[l])), bias=s.vec_src(n(self.bkeys[l])), act=ACT_SIGMOID,
                    out=self.act[l + 1], out_t=self.act_t[l + 1] if need_t else None, b_static=True)
@@ -99,11 +101,14 @@ class EncoderPlan(DevicePlan):
 
     def forward_backward(self) -> None:
         s, n = self.store, self._name
-        self._zero_grads_on_side()
-        with torch.cuda.stream(self.side):
-            self.losses["loss"].zero_()
-        self.forward()
-        self._join()
+        # no fill kernels in the step: the input cast clears the loss accumulator, the previous push
+        # cleared the accumulated (bias) gradients, every other gradient is overwritten
+        local_zero = not s.owner_zeroes_grads
+        if local_zero:
+            self._zero_grads_on_side()
+        self.forward(clear=self.losses["loss"])
+        if local_zero:
+            self._join()
         K.mse_sigmoid_grad(self.y, self.inputs["x"], self.losses["loss"], self.dz[4], self.dz_t[4],
                            s.grad(n(self.bkeys[3])))
         for l in range(3, -1, -1):
@@ -149,6 +154,8 @@ class GanPlan(DevicePlan):
         self.Din_fake, self.DinT_fake = self.Din.rows_view(B, 2 * B), self.DinT.cols_view(B, 2 * B)
         self.Din_real, self.DinT_real = self.Din.rows_view(0, B), self.DinT.cols_view(0, B)
         self.DH_fake = self.DH.rows_view(B, 2 * B)
+        # accumulated column sums; b_disc_out is overwritten by the loss kernel
+        store.zero_after_push([self._name(k) for k in ("b_disc_hidden1", "b_gen_out", "b_gen_hidden1")])
 
     def forward(self) -> None:
         s, n, B = self.store, self._name, self.B
@@ -169,9 +176,12 @@ class GanPlan(DevicePlan):
 
     def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
         s, n, B = self.store, self._name, self.B
-        self._zero_grads_on_side()
+        local_zero = not s.owner_zeroes_grads
+        if local_zero:
+            self._zero_grads_on_side()
         self.forward()
-        self._join()
+        if local_zero:
+            self._join()
         K.gan_loss_grad(self.logit, B, self.losses_t, self.d_disc, self.d_disc_t, self.d_gen,
                         s.grad(n("b_disc_out")) if disc else None)
         if disc:
@@ -321,6 +331,8 @@ class ScaledLstmPlan(DevicePlan):
         self.dlogits, self.dlogits_t = BMat(B, C, dev), BMat(C, B, dev)
         self.dh_top = torch.zeros(B, H, device=dev)
         self.h_last_t = BMat(H, B, dev)
+        # accumulated gradients (bias column sums); the big kernels' gradients are overwritten by their GEMMs
+        store.zero_after_push([self._name("out_b")] + [self._name("bias%d" % l) for l in range(L)])
 
     def _rows(self, m: BMat, t: int) -> BMat:
         return m.rows_view(t * self.B, (t + 1) * self.B)
@@ -357,7 +369,8 @@ class ScaledLstmPlan(DevicePlan):
         s, n, mdl, B = self.store, self._name, self.model, self.B
         T, H = mdl.T, mdl.H
         TB = T * B
-        s.zero_grads()
+        if not s.owner_zeroes_grads:
+            s.zero_grads()
         self.forward(train=True)
         K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits, self.dlogits_t,
                             s.grad(n("out_b")), self.correct)

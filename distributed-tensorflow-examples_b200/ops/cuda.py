@@ -150,6 +150,8 @@ _lib.register_signature("psb_lstm_bwd_head", [c_void_p, c_int, ctypes.POINTER(Ls
 _lib.register_signature("psb_lstm_head_scratch_floats", [c_int])      # small: fits the int return
 _lib.register_signature("psb_cast_transpose", [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
                                                c_void_p, c_int, c_void_p])
+_lib.register_signature("psb_cast_transpose_clear", [c_void_p, c_int, c_int, c_int, c_void_p, c_int,
+                                                     c_void_p, c_int, c_void_p, c_int, c_void_p])
 _lib.register_signature("psb_mse_sigmoid_grad", [c_void_p, c_int, c_void_p, c_int, c_int, c_int,
                                                  c_void_p, c_void_p, c_int, c_void_p, c_int,
                                                  c_void_p, c_void_p])
@@ -252,10 +254,19 @@ def lstm_bwd_head(w: BMat, saved: LstmSaved, dbias: torch.Tensor, h_last: BMat, 
 
 # --------------------------------------------------------------------------- cast / losses
 def cast_transpose(x: torch.Tensor, out: Optional[BMat] = None, out_t: Optional[BMat] = None,
-                   out_ptr: Optional[int] = None, out_t_ptr: Optional[int] = None) -> None:
+                   out_ptr: Optional[int] = None, out_t_ptr: Optional[int] = None,
+                   clear: Optional[torch.Tensor] = None) -> None:
     """fp32 [M,N] -> bf16 ``out`` [M,N] and/or ``out_t`` [N,M].  ``out_ptr``/``out_t_ptr``
-    redirect the write into a sub-block of a larger matrix (same leading dimensions)."""
+    redirect the write into a sub-block of a larger matrix (same leading dimensions).  ``clear``
+    is a small fp32 tensor (<= 256 elements, e.g. a loss accumulator) the kernel also zeroes."""
     M, N = x.shape
+    if clear is not None:
+        check(_lib.lib().psb_cast_transpose_clear(
+            x.data_ptr(), x.stride(0), M, N,
+            out_ptr if out_ptr is not None else _ptr(out), out.ld if out is not None else 0,
+            out_t_ptr if out_t_ptr is not None else _ptr(out_t), out_t.ld if out_t is not None else 0,
+            clear.data_ptr(), clear.numel(), current_stream_ptr()), "psb_cast_transpose_clear")
+        return
     check(_lib.lib().psb_cast_transpose(
         x.data_ptr(), x.stride(0), M, N,
         out_ptr if out_ptr is not None else _ptr(out), out.ld if out is not None else 0,

@@ -8,7 +8,7 @@ Three optimizers appear in the reference: ``RMSPropOptimizer(0.01)``
 An optimizer here is *data*: a kind id, hyper-parameters, and the names of the slot /
 non-slot variables it owns in the registry.  The arithmetic runs where the variable
 lives — in the native ps server (``csrc/ps_server.cpp``), in the fused push kernel
-(``csrc/push_fused.cu``), or in :func:`apply_reference` (the fp32 torch oracle used by
+(``csrc/push.cu``), or in :func:`apply_reference` (the fp32 torch oracle used by
 tests and by nothing on a hot path).
 """
 from __future__ import annotations

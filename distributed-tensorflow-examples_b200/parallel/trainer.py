@@ -23,14 +23,15 @@ from ..models import make_model
 from ..models.device_plans import make_plan
 from ..ops import _lib
 from ..placement import VariableRegistry, replica_device_setter
-from ..store.nvl import NvlStore
+from ..store.nvl import CTRL_GLOBAL_STEP, CTRL_STATUS, CTRL_WORDS, NvlStore
 
 
 class DeviceTrainer:
     def __init__(self, model_name: str, rank: int = 0, world: int = 1, group=None, mode: str = "sync",
                  batch: Optional[int] = None, seed: int = 0, use_graph: bool = True,
                  gan_update: str = "simultaneous", bcast: bool = True, plan_kwargs: Optional[dict] = None,
-                 model_kwargs: Optional[dict] = None):
+                 model_kwargs: Optional[dict] = None, partition: bool = True, timeout_s: float = 30.0,
+                 keep_grads: bool = False):
         if not torch.cuda.is_available():
             raise RuntimeError("DeviceTrainer needs a CUDA device; the CPU path is psb200.session.Session")
         _lib.lib()   # fail loudly if the kernel library is missing
@@ -38,7 +39,8 @@ class DeviceTrainer:
         self.registry = VariableRegistry(replica_device_setter(
             worker_device="/job:worker/task:%d" % rank, ps_tasks=world))
         self.model = make_model(model_name, **(model_kwargs or {})).build(self.registry)
-        self.store = NvlStore(self.model, self.registry, rank, world, group, mode=mode, bcast=bcast)
+        self.store = NvlStore(self.model, self.registry, rank, world, group, mode=mode, bcast=bcast,
+                              partition=partition, timeout_s=timeout_s, keep_grads=keep_grads)
         kw = dict(plan_kwargs or {})
         if self.model.name == "gan":
             kw.setdefault("seed", seed)
@@ -49,7 +51,8 @@ class DeviceTrainer:
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._loss_keys = list(self.plan.losses.keys())
         self._host_losses = torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory()
-        self._host_step = torch.zeros(1, dtype=torch.int32).pin_memory()
+        # one D2H brings back the push kernel's control block: status word and global_step
+        self._host_ctrl = torch.zeros(CTRL_WORDS, dtype=torch.int32).pin_memory()
         # one D2H per step for all losses: when the plan already keeps them next to each other the
         # copy reads them in place, otherwise they are gathered first
         self._dev_losses = self._adjacent_losses()
@@ -140,12 +143,21 @@ class DeviceTrainer:
                 self.plan.inputs[k].copy_(v.reshape(self.plan.inputs[k].shape), non_blocking=True)
         self.step_device()
         self._host_losses.copy_(self._dev_losses, non_blocking=True)
-        gs_rank = self.store.gs_owner if self.mode == "async" else self.rank
-        self._host_step.copy_(self.store.heap.tensor(self.store._gs_off, (1,), torch.int32, gs_rank),
-                              non_blocking=True)
+        self._host_ctrl.copy_(self._ctrl_src(), non_blocking=True)
         torch.cuda.current_stream().synchronize()
-        out = {k: float(self._host_losses[i]) for i, k in enumerate(self._loss_keys)}
-        out["global_step"] = int(self._host_step[0])
+        return self._result(self._host_losses, self._host_ctrl)
+
+    def _ctrl_src(self) -> torch.Tensor:
+        """The control block that holds the authoritative global_step: this rank's in sync mode
+        (lock-step replicas), the step owner's in async mode."""
+        gs_rank = self.store.gs_owner if self.mode == "async" else self.rank
+        return self.store.heap.tensor(self.store._ctrl_off, (CTRL_WORDS,), torch.int32, gs_rank)
+
+    def _result(self, losses: torch.Tensor, ctrl: torch.Tensor) -> Dict[str, float]:
+        if self.mode == "sync" or self.store.gs_owner == self.rank:
+            self.store.check_status(int(ctrl[CTRL_STATUS]))     # a peer died / stalled: raise, do not hang
+        out = {k: float(losses[i]) for i, k in enumerate(self._loss_keys)}
+        out["global_step"] = int(ctrl[CTRL_GLOBAL_STEP])
         return out
 
     # ---- pipelined stepping: input prefetch on a copy stream, results read one step late
@@ -156,7 +168,7 @@ class DeviceTrainer:
                 "seq": 0, "stream": torch.cuda.Stream(device=dev),
                 "stage": [{k: torch.empty_like(v) for k, v in self.plan.inputs.items()} for _ in range(2)],
                 "losses": [torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory() for _ in range(2)],
-                "gstep": [torch.zeros(1, dtype=torch.int32).pin_memory() for _ in range(2)],
+                "gstep": [torch.zeros(CTRL_WORDS, dtype=torch.int32).pin_memory() for _ in range(2)],
                 "h2d": [torch.cuda.Event() for _ in range(2)], "consumed": [torch.cuda.Event() for _ in range(2)],
                 "done": [torch.cuda.Event() for _ in range(2)], "pending": [False, False],
             }
@@ -166,9 +178,7 @@ class DeviceTrainer:
         p = self._pipe
         p["done"][k].synchronize()
         p["pending"][k] = False
-        out = {key: float(p["losses"][k][i]) for i, key in enumerate(self._loss_keys)}
-        out["global_step"] = int(p["gstep"][k][0])
-        return out
+        return self._result(p["losses"][k], p["gstep"][k])
 
     def step_async(self, batch: Dict[str, torch.Tensor]) -> Optional[Dict[str, float]]:
         """Pipelined :meth:`step`: enqueue this batch's H2D (copy stream, into one of two staging
@@ -193,8 +203,7 @@ class DeviceTrainer:
         p["consumed"][k].record(main)
         self.step_device()
         p["losses"][k].copy_(self._dev_losses, non_blocking=True)
-        gs_rank = self.store.gs_owner if self.mode == "async" else self.rank
-        p["gstep"][k].copy_(self.store.heap.tensor(self.store._gs_off, (1,), torch.int32, gs_rank), non_blocking=True)
+        p["gstep"][k].copy_(self._ctrl_src(), non_blocking=True)
         p["done"][k].record(main)
         p["pending"][k] = True
         p["seq"] += 1
@@ -223,7 +232,7 @@ class DeviceTrainer:
         return sum(v.numel() * v.element_size() for k, v in batch.items() if k in self.plan.inputs)
 
     def d2h_bytes_per_step(self) -> int:
-        return self._host_losses.numel() * 4 + 4
+        return self._host_losses.numel() * 4 + self._host_ctrl.numel() * 4
 
     def global_step(self) -> int:
         return self.store.global_step()

@@ -36,7 +36,8 @@ class PushSeg(Structure):
                 ("opt_kind", c_int32), ("lr", c_float), ("h1", c_float), ("h2", c_float),
                 ("eps", c_float), ("master", c_void_p), ("slot0", c_void_p), ("slot1", c_void_p),
                 ("beta_pow", c_void_p), ("w_off", c_int64), ("ld_w", c_int32), ("wt_off", c_int64),
-                ("ld_wt", c_int32), ("f_off", c_int64), ("home", c_int32), ("bcast", c_int32)]
+                ("ld_wt", c_int32), ("f_off", c_int64), ("home", c_int32), ("bcast", c_int32),
+                ("flags", c_uint32), ("nblocks", c_uint32)]
 
 
 class BetaUpdate(Structure):
@@ -49,51 +50,92 @@ class PushDesc(Structure):
                 ("n_arenas", c_int), ("inv_replicas", c_float), ("step_id", c_uint32),
                 ("local_ctrl", c_void_p), ("beta", BetaUpdate * 2), ("nbeta", c_int),
                 ("global_step", c_void_p), ("step_delta", c_int), ("async_sgd_atomic", c_int),
-                ("signal_params", c_int), ("blocks_per_seg", c_int), ("prof", c_void_p)]
+                ("signal_params", c_int), ("blocks_per_seg", c_int), ("prof", c_void_p),
+                ("phases", c_int), ("replicas", c_int), ("timeout_ns", c_uint64)]
+
+
+SEG_ZERO_GRAD = 1
+CTRL_WORDS = 64                      # PSB_PUSH_CTRL_WORDS
+CTRL_STEP, CTRL_STATUS, CTRL_ABORT, CTRL_APPLIED = 2, 3, 4, 7
+CTRL_GLOBAL_STEP = 48                # global_step lives in a spare word of the control block: one D2H reads both
+PH_SIGNAL_GRADS, PH_WAIT_GRADS, PH_TRY_GRADS, PH_APPLY, PH_SIGNAL_PARAMS, PH_WAIT_PARAMS, PH_EACH = 1, 2, 4, 8, 16, 32, 64
+STATUS_TEXT = {1: "timed out waiting for a peer's gradients", 2: "timed out waiting for a peer's parameters",
+               3: "aborted by the host"}
+
+
+class PeerTimeoutError(RuntimeError):
+    """A cross-GPU wait inside the push kernel ended on its deadline or on the abort word: a peer
+    rank is dead or stuck.  The step was not applied on this rank."""
 
 
 _lib.register_signature("psb_push_apply", [POINTER(PushDesc), c_void_p])
 _lib.register_signature("psb_wait_params", [c_void_p, c_int, c_uint32, c_void_p])
+_lib.register_signature("psb_push_commit", [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_uint64, c_void_p])
 
 
 class _VarLayout:
     __slots__ = ("spec", "rows", "cols", "grad_off", "master_off", "slot_offs", "w_off", "ld_w",
-                 "wt_off", "ld_wt", "f_off", "owner")
+                 "wt_off", "ld_wt", "f_off", "owner", "blocks")
 
 
 class NvlStore:
     """Parameter shards + gradient buffers of one rank, and the push launcher."""
 
     PAD_WORDS = 64
+    PARTITION_MIN_ELEMS = 8192
 
     def __init__(self, model: Model, registry: VariableRegistry, rank: int = 0, world: int = 1,
-                 group=None, mode: str = "sync", bcast: bool = True, device=None):
+                 group=None, mode: str = "sync", bcast: bool = True, device=None, partition: bool = True,
+                 timeout_s: float = 30.0, keep_grads: bool = False):
         if mode not in ("sync", "async"):
             raise ValueError("mode must be 'sync' or 'async'")
         self.model, self.registry = model, registry
         self.rank, self.world, self.group, self.mode, self.bcast = rank, world, group, mode, bcast
+        self.partition = partition and world > 1
+        self.timeout_ns = int(timeout_s * 1e9)
+        self.keep_grads = keep_grads          # tests/debugging: leave the gradients readable after the push
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self.layout: Dict[str, _VarLayout] = {}
         self._opt_of: Dict[str, Optimizer] = {}
         for op in model.train_ops:
             for n in op.var_list:
                 self._opt_of[n] = op.optimizer
+        self._zero_after_push = set()
         self._plan_heap()
         self.heap = SymmetricHeap(self._heap_bytes, rank, world, group, self.device)
         assert self.heap.alloc(self._heap_bytes, 256) == 0
         h = self.heap
         self.pad = h.tensor(self._pad_off, (self.PAD_WORDS,), torch.int32)
-        self.ctrl = h.tensor(self._ctrl_off, (4,), torch.int32)
+        self.ctrl = h.tensor(self._ctrl_off, (CTRL_WORDS,), torch.int32)
         self.grads = h.tensor(self._grad_off, (self._grad_elems,), torch.float32)
         self.global_step_t = h.tensor(self._gs_off, (1,), torch.int32)
         self.gs_owner = model.global_step.ps_task % world
         self.prof = torch.zeros(8, dtype=torch.int64, device=self.device)
         self._tables()
         self._seg_cache = {}
-        self._segs_refresh = self._build_segs(owned_only=True, peer_state=False, kind_override=-1)
         self._push_count = 0
+        self._abort_src = torch.ones(1, dtype=torch.int32).pin_memory()
+        self._abort_stream = None
 
     # ------------------------------------------------------------------ layout
+    def _row_blocks(self, rows: int, cols: int, home: int):
+        """Row blocks of one variable and their owners.  A variable stays whole on its home rank
+        (``replica_device_setter``'s round-robin, ``encoder:111-113``) unless it is big enough for the
+        reduction to matter; then it is cut into ``world`` runs of rows (multiples of four, so both
+        bf16 copies keep their 8-byte stores) owned by ranks ``home, home+1, ...`` -- a partitioned
+        variable in TF terms, same checkpoint name and shape."""
+        W = self.world
+        if not self.partition or rows * cols < self.PARTITION_MIN_ELEMS or rows < 4 * W:
+            return [(0, rows, home)]
+        per = (rows + W - 1) // W
+        per = (per + 3) // 4 * 4
+        out, r0, b = [], 0, 0
+        while r0 < rows:
+            r1 = min(rows, r0 + per)
+            out.append((r0, r1, (home + b) % W))
+            r0, b = r1, b + 1
+        return out
+
     def _plan_heap(self) -> None:
         cur = 0
 
@@ -104,8 +146,9 @@ class NvlStore:
             return off
 
         self._pad_off = take(self.PAD_WORDS * 4)
-        self._ctrl_off = take(16)
-        self._gs_off = take(16)
+        self._ctrl_off = take(CTRL_WORDS * 4)
+        self._wctrl_off = take(CTRL_WORDS * 4)          # worker-side words of the decoupled protocol
+        self._gs_off = self._ctrl_off + 4 * CTRL_GLOBAL_STEP
         # Adam beta powers: one {b1p, b2p} pair per Adam optimizer
         self._beta_off: Dict[int, int] = {}
         for k, op in enumerate(self.model.train_ops):
@@ -120,6 +163,7 @@ class NvlStore:
             L.spec = s
             L.rows, L.cols = (s.shape[0], s.shape[1]) if len(s.shape) == 2 else (1, s.numel)
             L.owner = s.ps_task % self.world
+            L.blocks = self._row_blocks(L.rows, L.cols, L.owner) if len(s.shape) == 2 else [(0, 1, L.owner)]
             L.grad_off = g
             g += round_up(s.numel, 4)
             self.layout[s.name] = L
@@ -159,40 +203,84 @@ class NvlStore:
         # single-entry tables for the async launch (world == 1 from the kernel's viewpoint)
         self._t_grads_self = torch.tensor([h.ptr(self._grad_off)], dtype=torch.int64, device=self.device)
 
+    def zero_after_push(self, names) -> None:
+        """Variables whose gradient producers ACCUMULATE (bias column sums, atomically added split-K
+        partials): the push kernel clears their gradients in every rank's buffer right after reading
+        them, which replaces a separate clear of the gradient buffer in every step."""
+        self._zero_after_push.update(names)
+        self._seg_cache = {}
+
+    @property
+    def owner_zeroes_grads(self) -> bool:
+        """True: the push kernel clears the accumulated gradients it has consumed (PSB_SEG_ZERO_GRAD);
+        False: the plans clear the gradient buffer themselves at the start of a step."""
+        return not self.keep_grads
+
     def _build_segs(self, owned_only: bool, peer_state: bool, kind_override: Optional[int],
                     op_names: Optional[List[str]] = None):
+        """Segment table (device) + grid.x.  One segment per owned row block."""
         h = self.heap
         segs = []
         wanted = None
         if op_names is not None:
             wanted = {n for op in self.model.train_ops if op.name in op_names for n in op.var_list}
         for name, L in self.layout.items():
-            if owned_only and L.owner != self.rank:
-                continue
             if wanted is not None and name not in wanted:
                 continue
             opt = self._opt_of[name]
             hv = opt.hyper_vector()
-            s = PushSeg()
-            s.grad_offset, s.numel, s.cols = L.grad_off, L.spec.numel, L.cols
-            s.opt_kind = opt.kind if kind_override is None else kind_override
-            s.lr, s.h1, s.h2, s.eps = hv
-            owner = L.owner if peer_state else self.rank
-            s.master = h.peer_ptr(owner, L.master_off)
-            s.slot0 = h.peer_ptr(owner, L.slot_offs[0]) if len(L.slot_offs) > 0 else None
-            s.slot1 = h.peer_ptr(owner, L.slot_offs[1]) if len(L.slot_offs) > 1 else None
-            if opt.kind == KIND_ADAM:
-                k = [i for i, op in enumerate(self.model.train_ops) if op.optimizer is opt][0]
-                brank = self._beta_owner(k) if peer_state else self.rank
-                s.beta_pow = h.peer_ptr(brank, self._beta_off[k])
-            s.w_off, s.ld_w, s.wt_off, s.ld_wt, s.f_off = L.w_off, L.ld_w, L.wt_off, L.ld_wt, L.f_off
-            s.home = L.owner if peer_state else self.rank
-            s.bcast = 1 if self.bcast else 0
-            segs.append(s)
+            for (r0, r1, owner) in L.blocks:
+                if owned_only and owner != self.rank:
+                    continue
+                two_d = len(L.spec.shape) == 2
+                e0 = r0 * L.cols if two_d else 0
+                numel = (r1 - r0) * L.cols if two_d else L.spec.numel
+                s = PushSeg()
+                s.grad_offset, s.numel, s.cols = L.grad_off + e0, numel, L.cols
+                s.opt_kind = opt.kind if kind_override is None else kind_override
+                s.lr, s.h1, s.h2, s.eps = hv
+                st_rank = owner if peer_state else self.rank
+                s.master = h.peer_ptr(st_rank, L.master_off + 4 * e0)
+                s.slot0 = h.peer_ptr(st_rank, L.slot_offs[0] + 4 * e0) if len(L.slot_offs) > 0 else None
+                s.slot1 = h.peer_ptr(st_rank, L.slot_offs[1] + 4 * e0) if len(L.slot_offs) > 1 else None
+                if opt.kind == KIND_ADAM:
+                    k = [i for i, op in enumerate(self.model.train_ops) if op.optimizer is opt][0]
+                    brank = self._beta_owner(k) if peer_state else self.rank
+                    s.beta_pow = h.peer_ptr(brank, self._beta_off[k])
+                s.w_off = L.w_off + r0 * L.ld_w if L.w_off >= 0 else -1
+                s.wt_off = L.wt_off + r0 if L.wt_off >= 0 else -1
+                s.ld_w, s.ld_wt, s.f_off = L.ld_w, L.ld_wt, L.f_off
+                s.home = L.owner            # bcast=0: every row block lands in the arena of the variable's home rank
+                s.bcast = 1 if self.bcast else 0
+                s.flags = SEG_ZERO_GRAD if (name in self._zero_after_push and kind_override is None
+                                            and self.owner_zeroes_grads) else 0
+                # rounds of work: one block iteration covers TU 32x32 tiles, or 256 threads x U groups of
+                # four (TU, U as in csrc/push.cu for this world's template bucket)
+                kw = 1 if peer_state else self.world        # legacy async launches run with world == 1
+                maxw = 1 << max(0, (kw - 1).bit_length())
+                if two_d:
+                    units = (((r1 - r0) + 31) // 32) * ((L.cols + 31) // 32)
+                    tu = 1 if maxw >= 8 else 2
+                    s.nblocks = max(1, (units + tu - 1) // tu)
+                else:
+                    per_iter = 256 * 4 * (1 if maxw >= 8 else (2 if maxw >= 4 else 4))
+                    s.nblocks = max(1, (numel + per_iter - 1) // per_iter)
+                segs.append(s)
+        # s.nblocks holds the rounds of work (one round = what one block does per loop iteration).
+        # Smallest number of rounds per block R such that the whole launch fits in one wave of
+        # 2 blocks per SM: small models then finish in a single round per block.
+        budget = 296
+        R = 1
+        while sum((s.nblocks + R - 1) // R for s in segs) > budget:
+            R += 1
+        gx = 1
+        for s in segs:
+            s.nblocks = max(1, (s.nblocks + R - 1) // R)
+            gx = max(gx, s.nblocks)
         arr = (PushSeg * max(len(segs), 1))(*segs)
         raw = bytes(arr) if segs else b"\0" * ctypes.sizeof(PushSeg)
         dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
-        return dev, len(segs)
+        return dev, len(segs), gx
 
     def _beta_owner(self, op_index: int) -> int:
         opt = self.model.train_ops[op_index].optimizer
@@ -241,6 +329,7 @@ class NvlStore:
         return self.heap.tensor(self._grad_off + 4 * L.grad_off, L.spec.shape, torch.float32)
 
     def owner(self, name: str) -> int:
+        """Home rank of a variable (of its first row block when it is partitioned)."""
         return self.layout[name].owner
 
     def master(self, name: str, rank: Optional[int] = None) -> torch.Tensor:
@@ -249,35 +338,54 @@ class NvlStore:
 
     # ------------------------------------------------------------------ variable access by checkpoint names
     def _locate(self, name: str):
-        """(offset, shape, dtype, owner rank) of any registry entry that has storage here."""
+        """(offset, shape, dtype, [(elem0, elem1, owner rank)]) of any registry entry that has storage here."""
         spec = self.registry[name]
         if name in self.layout:
             L = self.layout[name]
-            return L.master_off, spec.shape, torch.float32, L.owner
+            return L.master_off, spec.shape, torch.float32, self._runs(L)
         if spec.kind == "step":
-            return self._gs_off, (), torch.int32, self.gs_owner
+            return self._gs_off, (), torch.int32, [(0, 1, self.gs_owner)]
         if spec.kind == "slot":
             L = self.layout[spec.primary]
             idx = self._opt_of[spec.primary].slots[spec.primary].index(name)
-            return L.slot_offs[idx], spec.shape, torch.float32, L.owner
+            return L.slot_offs[idx], spec.shape, torch.float32, self._runs(L)
         if spec.kind == "nonslot":
             for k, op in enumerate(self.model.train_ops):
                 if name in op.optimizer.nonslots:
                     j = op.optimizer.nonslots.index(name)
-                    return self._beta_off[k] + 4 * j, (), torch.float32, self._beta_owner(k)
+                    return self._beta_off[k] + 4 * j, (), torch.float32, [(0, 1, self._beta_owner(k))]
         raise KeyError(name)
 
+    @staticmethod
+    def _runs(L: _VarLayout):
+        if len(L.spec.shape) != 2:
+            return [(0, max(1, L.spec.numel), L.owner)]
+        return [(r0 * L.cols, r1 * L.cols, owner) for (r0, r1, owner) in L.blocks]
+
     def read(self, name: str) -> torch.Tensor:
-        """Authoritative value (from the owner's HBM) as a CPU tensor."""
-        off, shape, dtype, owner = self._locate(name)
-        n = 1
-        for d in shape:
-            n *= d
-        return self.heap.tensor(off, (n,), dtype, owner).cpu().reshape(shape).clone()
+        """Authoritative value (every row block from its owner's HBM) as a CPU tensor."""
+        off, shape, dtype, runs = self._locate(name)
+        parts = [self.heap.tensor(off + 4 * e0, (e1 - e0,), dtype, owner).cpu() for (e0, e1, owner) in runs]
+        return torch.cat(parts).reshape(shape).clone()
 
     def read_all(self) -> Dict[str, torch.Tensor]:
         torch.cuda.synchronize()
         return {s.name: self.read(s.name) for s in self.registry}
+
+    def snapshot_async(self, stream: "torch.cuda.Stream") -> Dict[str, torch.Tensor]:
+        """Every variable copied owner-HBM -> pinned host memory on ``stream`` without stopping the
+        training stream (the checkpoint timer thread's read: like the reference's Saver it may see a
+        mixture of two consecutive steps, ``encoder:138,151``).  Synchronise ``stream`` before use."""
+        out = {}
+        with torch.cuda.stream(stream):
+            for s in self.registry:
+                off, shape, dtype, runs = self._locate(s.name)
+                n = runs[-1][1]
+                host = torch.empty(n, dtype=dtype).pin_memory()
+                for (e0, e1, owner) in runs:
+                    host[e0:e1].copy_(self.heap.tensor(off + 4 * e0, (e1 - e0,), dtype, owner), non_blocking=True)
+                out[s.name] = host.reshape(shape)
+        return out
 
     def assign(self, values: Dict[str, torch.Tensor], everywhere: bool = True) -> None:
         """Write values into the owners' state (the chief's init_op / checkpoint restore).
@@ -286,22 +394,42 @@ class NvlStore:
         for name, v in values.items():
             if name not in self.registry:
                 continue
-            off, shape, dtype, owner = self._locate(name)
+            off, shape, dtype, runs = self._locate(name)
             n = max(1, v.numel())
             src = v.to(dtype).reshape(n).to(self.device)
-            targets = {owner}
-            if everywhere:
-                targets.add(self.rank)
-            for r in targets:
-                self.heap.tensor(off, (n,), dtype, r).copy_(src)
+            for (e0, e1, owner) in runs:
+                targets = {owner}
+                if everywhere:
+                    targets.add(self.rank)
+                for r in targets:
+                    self.heap.tensor(off + 4 * e0, (e1 - e0,), dtype, r).copy_(src[e0:e1])
         torch.cuda.synchronize()
 
     def global_step(self) -> int:
         r = self.gs_owner if self.mode == "async" else self.rank
         return int(self.heap.tensor(self._gs_off, (1,), torch.int32, r).item())
 
+    # ------------------------------------------------------------------ failure containment
+    def status(self) -> int:
+        return int(self.ctrl[CTRL_STATUS].item())
+
+    def check_status(self, status: Optional[int] = None) -> None:
+        st = self.status() if status is None else status
+        if st != 0:
+            raise PeerTimeoutError("rank %d: push kernel %s (status %d)" % (self.rank, STATUS_TEXT.get(st, "failed"), st))
+
+    def abort(self) -> None:
+        """Make every cross-GPU wait of a running or future push kernel on this rank give up (a
+        supervisor calls this when a peer is known to be gone).  Safe while a kernel is spinning:
+        the write goes through a separate stream."""
+        if self._abort_stream is None:
+            self._abort_stream = torch.cuda.Stream(device=self.device)
+        with torch.cuda.stream(self._abort_stream):
+            self.ctrl[CTRL_ABORT:CTRL_ABORT + 1].copy_(self._abort_src, non_blocking=True)
+        self._abort_stream.synchronize()
+
     # ------------------------------------------------------------------ push
-    def _desc(self, segs, nseg: int, sync: bool, step_delta: int, with_beta: bool,
+    def _desc(self, segs, nseg: int, gx: int, sync: bool, step_delta: int, with_beta: bool,
               op_names: Optional[List[str]] = None) -> PushDesc:
         d = PushDesc()
         d.segs, d.nseg = segs.data_ptr(), nseg
@@ -310,10 +438,9 @@ class NvlStore:
         d.n_arenas = self.world
         d.local_ctrl = self.ctrl.data_ptr()
         d.step_id = 0
-        big = self._grad_elems > (4 << 20)          # large shards: two CTAs per SM to keep NVLink loads in flight
-        cap = 296 if big else 148
-        d.blocks_per_seg = max(1, min(cap, cap // max(1, nseg))) if (sync and self.world > 1) else (cap // max(1, nseg) if big else 48)
+        d.blocks_per_seg = gx
         d.prof = self.prof.data_ptr()
+        d.timeout_ns = self.timeout_ns
         if sync:
             d.grad_ptrs, d.world, d.rank = self._t_grads.data_ptr(), self.world, self.rank
             d.inv_replicas = 1.0 / self.world
@@ -350,20 +477,24 @@ class NvlStore:
         if key not in self._seg_cache:
             self._seg_cache[key] = self._build_segs(owned_only=sync, peer_state=not sync,
                                                     kind_override=None, op_names=op_names)
-        segs, n = self._seg_cache[key]
+        segs, n, gx = self._seg_cache[key]
         delta = sum(1 for op in self.model.train_ops if op.increments_global_step and
                     (op_names is None or op.name in op_names))
-        d = self._desc(segs, n, sync, delta, True, op_names)
+        d = self._desc(segs, n, gx, sync, delta, True, op_names)
         _lib.check(_lib.lib().psb_push_apply(ctypes.byref(d), stream), "psb_push_apply")
         self._push_count += 1
 
     def refresh_copies(self) -> None:
         """Re-derive every bf16/fp32 compute copy from the owners' master weights (after the
         chief's init or a checkpoint restore).  Collective in sync geometry."""
-        segs, n = self._segs_refresh
-        d = self._desc(segs, n, True, 0, False)
+        key = "refresh"
+        if key not in self._seg_cache:
+            self._seg_cache[key] = self._build_segs(owned_only=True, peer_state=False, kind_override=-1)
+        segs, n, gx = self._seg_cache[key]
+        d = self._desc(segs, n, gx, True, 0, False)
         _lib.check(_lib.lib().psb_push_apply(ctypes.byref(d), _lib.current_stream_ptr()), "psb_push_apply(refresh)")
         torch.cuda.synchronize()
+        self.check_status()
 
     def push_profile(self, reset: bool = True) -> Dict[str, float]:
         """Average microseconds per push spent (a) waiting for every rank's gradients, (b)

@@ -144,6 +144,16 @@ class TcpStore:
         self._of(gs).queue_enqueue_many(SYNC_TOKEN_QUEUE, [new_step] * self.num_workers)
         return new_step
 
+    def release_sync_waiters(self) -> None:
+        """Chief shutdown in sync mode: no aggregate will ever be applied again, so hand every worker
+        a sentinel token (-1).  A worker blocked in :meth:`push_sync` returns -1, leaves its loop and
+        sends its done token -- otherwise the ps tasks would wait for it forever."""
+        gs = self.model.global_step
+        try:
+            self._of(gs).queue_enqueue_many(SYNC_TOKEN_QUEUE, [-1] * self.num_workers)
+        except Exception:
+            pass
+
     # ------------------------------------------------------------------ done queues (C6)
     def enqueue_done(self, capacity: int) -> None:
         """``for op in enq_ops: sess.run(op)`` — one token onto every ps task's queue

@@ -58,9 +58,12 @@ class Supervisor:
     def stop(self) -> None:
         """Idempotent (the reference calls it twice: leaving managed_session and ``encoder:176``)."""
         self._stop.set()
+        had_runner = any(t.name == "SyncReplicasQueueRunner" for t in self._threads)
         for t in self._threads:
             t.join(timeout=10.0)
         self._threads = []
+        if had_runner and hasattr(self.store, "release_sync_waiters"):
+            self.store.release_sync_waiters()      # the aggregation runner is gone: unblock waiting workers
 
     # ---- session bring-up ------------------------------------------------------------
     def prepare_or_wait_for_session(self) -> None:

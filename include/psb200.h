@@ -176,6 +176,10 @@ int psb_transpose_bf16(const void* in, int ld_in, int R, int C, void* out, int l
  * ref: feed_dict of the float32 placeholders, encoder:165, gan:192-194, lstm:128. */
 int psb_cast_transpose(const float* in, int ld_in, int M, int N, void* out, int ld_out,
                        void* out_t, int ld_t, void* stream);
+/* The same, and the kernel also zeroes clear[0..n_clear) (n_clear <= 256): as the first kernel of
+ * a step it resets the loss accumulators the later kernels add into, so a step needs no fill. */
+int psb_cast_transpose_clear(const float* in, int ld_in, int M, int N, void* out, int ld_out,
+                             void* out_t, int ld_t, float* clear, int n_clear, void* stream);
 
 /* MSE between the sigmoid output y (fp32 [M, ld_y]) and the target x (fp32 [M, ld_x]):
  * *loss += mean((x-y)^2) (caller zeroes it), dz = dLoss/d(pre-activation) as bf16 [M, ld_dz],
@@ -218,7 +222,13 @@ typedef struct psb_push_seg {
     int64_t f_off;          /* element offset of an fp32 copy [numel] in the fp32 arena, -1 = none */
     int32_t home;           /* index into arena_ptrs that receives the copies when !bcast */
     int32_t bcast;          /* 1: write the copies into every rank's arena (push-mode all-gather) */
+    uint32_t flags;         /* PSB_SEG_* */
+    uint32_t nblocks;       /* blocks of the launch (of grid.x) that share this segment; 0 = all */
 } psb_push_seg_t;
+/* After reading them, overwrite this segment's gradients with zero in EVERY rank's gradient
+ * buffer, so producers that accumulate (bias column sums, split-K partial sums) need no separate
+ * clear before the next step. */
+#define PSB_SEG_ZERO_GRAD 1u
 
 typedef struct psb_beta_update {
     float* beta_pow;        /* {beta1_power, beta2_power} */
@@ -237,18 +247,42 @@ typedef struct psb_push_desc {
     float inv_replicas;              /* 1 / replicas_to_aggregate */
     uint32_t step_id;                /* monotone token, first call = 1; 0 = use local_ctrl[2] + 1
                                         (lets a captured CUDA graph replay the launch) */
-    uint32_t* local_ctrl;            /* DEVICE, 4 zero-initialised words private to this rank */
+    uint32_t* local_ctrl;            /* DEVICE, PSB_PUSH_CTRL_WORDS zero-initialised words private to this rank:
+                                        [2] last step token, [3] status (PSB_PUSH_ST_*, sticky), [4] abort request
+                                        (a non-zero value written by the host ends every wait), [7] updates applied */
     psb_beta_update_t beta[2];
     int nbeta;
     int32_t* global_step;            /* incremented by step_delta by the last block (NULL = not here) */
     int step_delta;
     int async_sgd_atomic;
-    int signal_params;               /* publish (and wait for) params-ready on the pads */
-    int blocks_per_seg;              /* 0 = default */
+    int signal_params;               /* publish (and wait for) params-ready on the pads (when phases == 0) */
+    int blocks_per_seg;              /* grid.x; a segment uses its first `nblocks` of them.  0 = default */
     uint64_t* prof;                  /* optional DEVICE [8] u64, zeroed by the caller: the kernel adds the
                                         nanoseconds it spent waiting for gradients [4], reducing+applying [5],
                                         waiting for parameters [6], and the call count [7] (globaltimer) */
+    int phases;                      /* PSB_PUSH_* bits; 0 = the fused step: signal + wait for all gradients, apply,
+                                        and (signal_params) signal + wait for all parameters */
+    int replicas;                    /* R of N: aggregate the first `replicas` gradients to arrive, mean over those
+                                        actually taken; gradients that arrive later are never read.  <= 0 or >= world: all */
+    uint64_t timeout_ns;             /* bound on every cross-GPU wait (globaltimer); 0 = none.  On expiry the kernel
+                                        applies nothing, sets local_ctrl[3] and returns */
 } psb_push_desc_t;
+
+#define PSB_PUSH_CTRL_WORDS 64
+/* phases */
+#define PSB_PUSH_SIGNAL_GRADS 1   /* publish "my gradients for this step are complete" to every pad */
+#define PSB_PUSH_WAIT_GRADS 2     /* block until `replicas` ranks have published theirs */
+#define PSB_PUSH_TRY_GRADS 4      /* do not block: if fewer have, apply nothing and return (ps service polling) */
+#define PSB_PUSH_APPLY 8
+#define PSB_PUSH_SIGNAL_PARAMS 16 /* publish "parameters of this step are in place" */
+#define PSB_PUSH_WAIT_PARAMS 32   /* block until every owner has */
+#define PSB_PUSH_EACH 64          /* async owner-side apply: one optimizer step per newly arrived gradient, in rank
+                                     order, then acknowledge each sender (pad word 32 + owner) */
+/* local_ctrl[3] */
+#define PSB_PUSH_ST_OK 0
+#define PSB_PUSH_ST_TIMEOUT_GRADS 1
+#define PSB_PUSH_ST_TIMEOUT_PARAMS 2
+#define PSB_PUSH_ST_ABORTED 3
 
 /* Reduce-scatter + optimizer apply (+ all-gather of the bf16 copies) in one kernel over peer
  * memory; see csrc/push.cu.  Allocates nothing.
@@ -259,23 +293,40 @@ int psb_push_apply(const psb_push_desc_t* desc, void* stream);
  * start-up, a latency path where cudaMalloc's implicit synchronisation is unacceptable).
  * This entry point has no counterpart in the reference; it exists only for those callers.
  * The kernel's control words, the segment table and the pointer tables live in one static
- * device array inside the library image (about 7 KiB per GPU, held until process exit), so
- * the tables are given as HOST arrays: host_segs[nseg], and host_grad_ptrs[world],
+ * device array inside the library image (8960 bytes = 8.75 KiB per GPU, held until process
+ * exit), so the tables are given as HOST arrays: host_segs[nseg], and host_grad_ptrs[world],
  * host_arena_ptrs[n_arenas], host_farena_ptrs[n_arenas], host_pad_ptrs[world] (may be NULL
- * when world == 1).  Of `desc`, the fields segs, grad_ptrs, arena_ptrs, farena_ptrs,
- * pad_ptrs and local_ctrl are ignored; all others mean what they mean for psb_push_apply.
+ * when world == 1); they are copied with cudaMemcpyAsync on `stream`, so keep them valid and
+ * unchanged until the stream has passed those copies.  Of `desc`, the fields segs, grad_ptrs,
+ * arena_ptrs, farena_ptrs, pad_ptrs and local_ctrl are ignored; all others mean what they mean
+ * for psb_push_apply.
  * Limits: nseg <= PSB_NOALLOC_MAX_SEGS, world and n_arenas <= PSB_NOALLOC_MAX_WORLD; beyond
- * them the call fails with an error text and launches nothing.
+ * them the call fails with an error text and launches nothing.  blocks_per_seg is capped at 64.
  * The first call on a device resolves the array's device address and caches it: make that
  * call before any stream capture.  Calls on one device share the array (the finished-block
- * counter is cleared per call, the step token is kept), so calls that overlap on the GPU
- * race: serialise them.  Calls no cudaMalloc/cudaFree and no allocating library routine. */
+ * counter is cleared per call; the step token, launch number and status word are kept), so
+ * calls that overlap on the GPU race: serialise them.  Because the step token is kept for the
+ * life of the process, explicit step ids (desc->step_id != 0) must keep increasing per device
+ * across all users of this entry point, and one set of signal pads must be driven through
+ * EITHER this entry point OR psb_push_apply, never alternately: their automatic step tokens are
+ * separate (static array here, the caller's local_ctrl there) and would diverge.
+ * Calls no cudaMalloc/cudaFree and no allocating library routine. */
 #define PSB_NOALLOC_MAX_SEGS 64
 #define PSB_NOALLOC_MAX_WORLD 16
 int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
                            const float* const* host_grad_ptrs, void* const* host_arena_ptrs,
                            float* const* host_farena_ptrs, uint32_t* const* host_pad_ptrs,
                            const psb_push_desc_t* desc, void* stream);
+/* Worker half of the decoupled protocol (the owner half is psb_push_apply with PSB_PUSH_TRY_GRADS,
+ * launched by the ps service).  worker_ctrl: PSB_PUSH_CTRL_WORDS zeroed device words.
+ *   async_mode 0: publish gradients for token worker_ctrl[2] (first = 1), wait until every owner has
+ *                 applied an aggregate >= token, adopt min(applied)+1 as the next token -- a worker
+ *                 that fell behind skips ahead and its late gradient is dropped as stale;
+ *   async_mode 1: wait == 0 publishes gradient number worker_ctrl[2]+1; wait == 1 blocks until every
+ *                 owner has acknowledged gradient number worker_ctrl[2] (buffer free to overwrite).
+ * ref: token_queue dequeue / accumulator apply_grad of SyncReplicasOptimizer; plain minimize(). */
+int psb_push_commit(uint32_t* const* pad_ptrs, int world, int rank, uint32_t* worker_ctrl,
+                    int async_mode, int wait, uint64_t timeout_ns, void* stream);
 /* Block the stream until every rank has published params-ready >= step_id on `pad`. */
 int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream);
 

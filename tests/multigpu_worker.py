@@ -43,9 +43,9 @@ def main():
     if a.model == "lstm" and a.pull_from_owner:
         kw["pull_from_owner"] = True
 
-    def run_once():
+    def run_once(keep_grads=False):
         tr = DeviceTrainer(a.model, rank, world, group, mode=a.mode, seed=5, plan_kwargs=kw,
-                           bcast=not a.pull_from_owner)
+                           bcast=not a.pull_from_owner, keep_grads=keep_grads)
         values = tr.registry.initial_values(5)
         if a.model == "encoder":
             for s in tr.registry.trainable():
@@ -93,7 +93,9 @@ def main():
         dist.destroy_process_group()
         return
 
-    tr, values, res = run_once()
+    # first run keeps the gradients readable (the plan clears them itself); the re-run below lets the
+    # push kernel clear the consumed gradients in every rank's buffer: both must agree bit for bit
+    tr, values, res = run_once(keep_grads=True)
     model = tr.model
     if a.mode == "sync":
         assert res["global_step"] == model.steps_per_run(), res

@@ -171,9 +171,49 @@ def test_ps_runtime_accumulator_mean_and_stale_drop(ps):
     t.join(5)
     assert done == [2]
     assert torch.allclose(c.var_read("Variable", (4,), torch.float32), torch.full((4,), -3.0))   # w -= mean
-    c.acc_set_step("Variable", 1)
+    # the take itself advanced the accumulator's step (no window in which a backup worker's old
+    # gradient could slip into the next aggregate before acc_set_step arrives)
     assert c.acc_apply("Variable", torch.ones(4), 0) is False     # stale: dropped
-    assert c.stats()["stale_dropped"] == 1
+    c.acc_set_step("Variable", 1)
+    assert c.acc_apply("Variable", torch.ones(4), 0) is False
+    assert c.acc_apply("Variable", torch.ones(4), 1) is True
+    assert c.stats()["stale_dropped"] == 2
+
+
+def test_ps_runtime_survives_malformed_requests(ps):
+    """Requests a buggy or hostile client could send must be answered with an error, not crash the
+    ps process: slot counts that do not match the optimizer kind, missing slots in the sync path,
+    applies to uninitialised variables, absurd variable sizes."""
+    import struct
+    from psb200.control.client import OP_ACC_TAKE_APPLY, OP_APPLY, OP_VAR_DECLARE
+    c = PsClient(ps.target)
+    c.var_declare("w", (4,), torch.float32)
+    c.var_assign("w", torch.zeros(4))
+    c.var_declare("s", (4,), torch.float32)
+    c.var_assign("s", torch.zeros(4))
+    g = torch.ones(4)
+    hdr = lambda kind, slots: PsClient._apply_header(kind, [0.1, 0.9, 0.9, 1e-8], (0.9, 0.999), slots)   # noqa: E731
+    for kind, slots in ((0, ["s"]), (1, []), (2, ["s"]), (1, ["s", "nope"]), (7, [])):
+        with pytest.raises(PsError):
+            c._call(OP_APPLY, "w", hdr(kind, slots), "apply", tail=memoryview(g.numpy()).cast("B"))
+    c.acc_declare("w")
+    c.acc_apply("w", g, 0)
+    for kind, slots in ((2, []), (1, ["s"])):
+        with pytest.raises(PsError):
+            c._call(OP_ACC_TAKE_APPLY, "w", struct.pack("<I", 1) + hdr(kind, slots), "take")
+    c.var_declare("u", (4,), torch.float32)                     # never assigned
+    c.acc_declare("u")
+    with pytest.raises(PsError):
+        c._call(OP_ACC_TAKE_APPLY, "u", struct.pack("<I", 0) + hdr(0, []), "take")
+    with pytest.raises(PsError):                                # 2^40 x 2^40 elements
+        c._call(OP_VAR_DECLARE, "huge", struct.pack("<IIQQ", 0, 2, 1 << 40, 1 << 40), "declare")
+    with pytest.raises(PsError):                                # 2^31 elements x 4 B: bad_alloc or refused
+        c._call(OP_VAR_DECLARE, "huge2", struct.pack("<IIQ", 0, 1, (1 << 32) + 1), "declare")
+    # the server is still alive and consistent
+    c.ping()
+    assert torch.equal(c.var_read("w", (4,), torch.float32), torch.zeros(4))
+    # a closed connection's descriptor is forgotten: stopping the server later cannot hit a reused fd
+    PsClient(ps.target).close()
 
 
 def test_dtype_flag_rounds_weight_matrices_only():

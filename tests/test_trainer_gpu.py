@@ -40,7 +40,7 @@ def test_one_step_matches_oracle(name, use_graph):
     kw = {"device_noise": False} if name == "gan" else {}
     if name == "lstm_unfused_head":      # head as separate kernels (the evaluation path's kernels)
         name, kw = "lstm", {"fuse_head": False}
-    tr = DeviceTrainer(name, use_graph=use_graph, seed=3, plan_kwargs=kw)
+    tr = DeviceTrainer(name, use_graph=use_graph, seed=3, plan_kwargs=kw, keep_grads=True)   # gradients are read back below
     try:
         values = tr.registry.initial_values(3)
         if name == "encoder":           # N(0,1) init saturates every sigmoid; scale for a meaningful check

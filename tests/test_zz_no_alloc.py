@@ -114,7 +114,7 @@ def test_noalloc_entry_matches_regular_entry_twice():
     t_grads = torch.tensor([A["grads"].data_ptr()], dtype=torch.int64, device="cuda")
     t_arena = torch.tensor([A["arena"].data_ptr()], dtype=torch.int64, device="cuda")
     t_farena = torch.tensor([A["farena"].data_ptr()], dtype=torch.int64, device="cuda")
-    ctrl = torch.zeros(4, dtype=torch.int32, device="cuda")
+    ctrl = torch.zeros(64, dtype=torch.int32, device="cuda")    # PSB_PUSH_CTRL_WORDS
     # no-alloc entry point: host tables only
     P = ctypes.c_void_p * 1
     h_grads, h_arena, h_farena = P(B["grads"].data_ptr()), P(B["arena"].data_ptr()), P(B["farena"].data_ptr())
@@ -139,6 +139,49 @@ def test_noalloc_entry_matches_regular_entry_twice():
         assert torch.allclose(A["beta"], B["beta"]) and int(A["gstep"]) == int(B["gstep"]) == call + 1
     # the update did something: Adam's beta powers advanced twice
     assert abs(float(B["beta"][0]) - 0.9 ** 3) < 1e-6
+
+
+def test_noalloc_entry_takes_any_segment_count_up_to_its_limit():
+    """40 segments with the default number of blocks per segment: the static array holds up to 64
+    segment records, and no other limit may turn a request of that size away (an earlier version
+    refused it with a grid-size check that only multi-GPU launches need)."""
+    from psb200.ops import _lib
+    import psb200.store.nvl as nvl
+    L = _lib.lib()
+    fn = L.psb_push_apply_noalloc
+    fn.restype = ctypes.c_int
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                   ctypes.c_void_p, ctypes.POINTER(nvl.PushDesc), ctypes.c_void_p]
+    nseg, n = 40, 52
+    g = torch.Generator().manual_seed(3)
+    master = torch.randn(nseg * n, generator=g).cuda()
+    want = master.clone()
+    grads = torch.randn(nseg * n, generator=g).cuda()
+    farena = torch.zeros(nseg * n, device="cuda")
+    arena = torch.zeros(128, dtype=torch.bfloat16, device="cuda")
+    gstep = torch.zeros(1, dtype=torch.int32, device="cuda")
+    segs = (nvl.PushSeg * nseg)()
+    for i in range(nseg):
+        s = segs[i]
+        s.grad_offset, s.numel, s.cols = i * n, n, n
+        s.opt_kind, s.lr = 0, 0.5
+        s.master = master.data_ptr() + 4 * i * n
+        s.w_off = s.wt_off = -1
+        s.f_off = i * n
+        s.home, s.bcast = 0, 1
+    d = nvl.PushDesc()
+    d.world, d.rank, d.n_arenas, d.inv_replicas = 1, 0, 1, 1.0
+    d.global_step, d.step_delta = gstep.data_ptr(), 1
+    d.blocks_per_seg = 0                                  # default
+    P = ctypes.c_void_p * 1
+    stream = torch.cuda.current_stream().cuda_stream
+    for call in range(2):
+        _lib.check(fn(segs, nseg, P(grads.data_ptr()), P(arena.data_ptr()), P(farena.data_ptr()), None,
+                      ctypes.byref(d), stream), "psb_push_apply_noalloc")
+        want -= 0.5 * grads
+        torch.cuda.synchronize()
+        assert torch.allclose(master, want, rtol=2e-4, atol=1e-7), call
+        assert torch.equal(farena, master) and int(gstep) == call + 1
 
 
 def test_noalloc_entry_rejects_oversized_requests():
