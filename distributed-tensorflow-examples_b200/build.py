@@ -21,7 +21,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
 
-KERNEL_SOURCES = ["lib.cu", "gemm.cu", "lstm.cu", "losses.cu", "push.cu", "peer.cu", "lstm_cell.cu"]
+KERNEL_SOURCES = ["lib.cu", "gemm.cu", "lstm.cu", "losses.cu", "push.cu", "peer.cu", "lstm_cell.cu", "ps_service.cu"]
 PS_SOURCES = ["ps_server.cpp", "tf_bundle.cpp"]
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",

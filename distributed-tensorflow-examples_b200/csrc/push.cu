@@ -111,6 +111,13 @@ __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t* p) {
     return r;
 }
 __device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+// Release fence for what this block wrote (possibly into peers' memory) before it is counted as done.
+// With peers it must be system scope; alone on the box, device scope is enough and much cheaper
+// (a system-scope fence costs about 3 us here).
+__device__ __forceinline__ void release_fence(bool peers) {
+    if (peers) asm volatile("fence.acq_rel.sys;" ::: "memory");
+    else asm volatile("fence.acq_rel.gpu;" ::: "memory");
+}
 
 // Four consecutive floats: one 128-bit access when the group is whole and aligned, otherwise
 // `nvalid` scalar ones (rows whose length is not a multiple of four, the tail of a vector).
@@ -230,9 +237,12 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
     const bool has_seg = static_cast<int>(blockIdx.y) < a.nseg;
     psb_push_seg_t s;
     if (has_seg) s = a.segs[blockIdx.y];
-    uint32_t nb = 0;
-    if (has_seg) nb = (s.nblocks != 0 && s.nblocks < gridDim.x) ? s.nblocks : gridDim.x;
-    const bool has_work = has_seg && blockIdx.x < nb && (a.phases & PSB_PUSH_APPLY);
+    uint32_t nb = 0, bx = 0;
+    if (has_seg) {
+        nb = s.nblocks != 0 ? s.nblocks : gridDim.x;
+        bx = s.block_x + blockIdx.x;
+    }
+    const bool has_work = has_seg && bx < nb && (a.phases & PSB_PUSH_APPLY);
     if (tid < kMaxWorld) {
         if (tid < a.world) s_grad[tid] = a.grad_ptrs[tid];
         if (tid < a.n_arenas) {
@@ -258,7 +268,8 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
     // ---------------- cross-GPU: the gradients this launch consumes are in place
     if (a.world > 1) {
         if (first_block && (a.phases & PSB_PUSH_SIGNAL_GRADS) && tid < a.world) {
-            __threadfence_system();
+            // the gradients were written by earlier kernels of this stream: complete and in L2 (where
+            // peers read them) since those kernels ended; the release store needs no extra fence
             st_release_sys(a.pad_ptrs[tid] + kPadGrads + a.rank, a.step_id);
         }
         if (all_ranks && (a.phases & PSB_PUSH_WAIT_GRADS)) {
@@ -349,7 +360,7 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
             const int ty = tid >> 3, tx4 = (tid & 7) * 4;
             const bool v4 = aligned && (cols % 4 == 0);
             constexpr int TU = MAXW >= 8 ? 1 : 2;      // tiles per iteration (register budget: TU * MAXW peer loads)
-            for (int t0 = blockIdx.x * TU; t0 < ntiles; t0 += nb * TU) {
+            for (int t0 = bx * TU; t0 < ntiles; t0 += nb * TU) {
                 float4 t[TU][MAXW];
                 float4 w[TU], v0[TU], v1[TU];
                 bool live[TU];
@@ -451,7 +462,7 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
             // ---- vectors (biases, flat shards): groups of four, U groups per thread per iteration
             constexpr int U = MAXW >= 8 ? 1 : (MAXW >= 4 ? 2 : 4);   // >= 4 (8 from MAXW = 2) 128-bit loads in flight per thread
             const uint32_t n4 = (s.numel + 3) / 4;
-            for (uint32_t base = blockIdx.x * (kPushThreads * U); base < n4; base += nb * (kPushThreads * U)) {
+            for (uint32_t base = bx * (kPushThreads * U); base < n4; base += nb * (kPushThreads * U)) {
                 float4 t[U][MAXW];
                 float4 w[U], v0[U], v1[U];
                 int nv[U];
@@ -515,9 +526,12 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
 
     // ---------------- completion: last block finishes the step
     __syncthreads();
+    // remote writes happen when there are peers' arenas / gradient buffers to write, or (legacy async)
+    // when master and slots are peer pointers
+    const bool peers = a.world > 1 || a.n_arenas > 1 || a.async_sgd_atomic;
     if (tid == 0) {
         if (bad_grads) atomicMax(ctrl + kCtrlStatus, static_cast<uint32_t>(bad_grads));
-        __threadfence_system();
+        release_fence(peers);
         const uint32_t prev = atomicAdd(ctrl + kCtrlDone, 1u);
         is_last = (prev == total_blocks - 1);
     }
@@ -545,7 +559,9 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
                     for (int r = 0; r < a.world; ++r)
                         if ((mask >> r) & 1u) ctrl[kCtrlConsumed + r] = ctrl[kCtrlConsumed + 16 + r];
             }
-            __threadfence_system();
+            // no fence here: the release stores below order everything this block has seen
+            // (bar.sync makes thread 0's writes part of the signalling threads' causality order)
+            release_fence(false);
         }
         __syncthreads();
         if (a.world > 1 && applied && tid < a.world) {
@@ -711,12 +727,12 @@ extern "C" int psb_push_apply(const psb_push_desc_t* d, void* stream) {
     a.farena_ptrs = d->farena_ptrs; a.pad_ptrs = d->pad_ptrs; a.local_ctrl = d->local_ctrl;
     fill_args(a, d);
     int gx = d->blocks_per_seg > 0 ? d->blocks_per_seg : 16;
-    if (gx > 592) gx = 592;
+    if (gx > 1024) gx = 1024;
+    if (d->nseg > 65535) return fail(PSB_ERR_LIMIT, "psb_push_apply: at most 65535 table entries");
     dim3 grid(gx, d->nseg > 0 ? d->nseg : 1);
-    // blocks of one launch wait for each other's decision (R of N) and for peers: all of them must be
-    // resident (4 x 256 threads per SM fit in registers and shared memory)
-    if (d->world > 1 && grid.x * grid.y > 592)
-        return fail(PSB_ERR_LIMIT, "psb_push_apply: grid %u x %u would not be co-resident", grid.x, grid.y);
+    // No co-residency requirement: a block only ever waits for peers' block (0,0) -- which is in the
+    // first wave of its grid and waits for nobody in its own grid -- and the last block to finish for
+    // the owners' final flags.
     rc = launch_push(a, grid, static_cast<cudaStream_t>(stream), true);
     if (rc != PSB_OK) return rc;
     return after_launch("push_apply");

@@ -55,6 +55,8 @@ class Flags:
     recovery_wait_secs: float = 1.0    # non-chief polling period (TF default is 30 s)
     batch_size: int = 0                # 0 -> the script's module constant
     checkpoint_format: str = "psb200"  # bundle written by the chief: "psb200" (JSON index) | "tf" (TF V2 bundle)
+    async_apply: str = "worker"        # nvl async: "worker" (remote read-modify-write on the owner's HBM) | "owner" (ps service thread applies)
+    peer_timeout_secs: float = 30.0    # nvl: bound on every cross-GPU wait inside the push kernel
     extra: List[str] = field(default_factory=list)
 
     def ps_list(self) -> List[str]:
@@ -106,6 +108,8 @@ def parse_flags(argv: Optional[Sequence[str]] = None, prog: Optional[str] = None
         raise SystemExit("--dtype must be 'fp32' or 'bf16'")
     if fl.checkpoint_format not in ("psb200", "tf"):
         raise SystemExit("--checkpoint_format must be 'psb200' or 'tf'")
+    if fl.async_apply not in ("worker", "owner"):
+        raise SystemExit("--async_apply must be 'worker' or 'owner'")
     if fl.gan_update not in ("simultaneous", "alternating"):
         raise SystemExit("--gan_update must be 'simultaneous' or 'alternating'")
     return fl

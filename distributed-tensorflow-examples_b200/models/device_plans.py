@@ -103,12 +103,13 @@ class EncoderPlan(DevicePlan):
         s, n = self.store, self._name
         # no fill kernels in the step: the input cast clears the loss accumulator, the previous push
         # cleared the accumulated (bias) gradients, every other gradient is overwritten
-        local_zero = not s.owner_zeroes_grads
+        local_zero = not s.owner_zeroes_grads and not s.zero_in_before_grads
         if local_zero:
             self._zero_grads_on_side()
         self.forward(clear=self.losses["loss"])
         if local_zero:
             self._join()
+        s.before_grads()
         K.mse_sigmoid_grad(self.y, self.inputs["x"], self.losses["loss"], self.dz[4], self.dz_t[4],
                            s.grad(n(self.bkeys[3])))
         for l in range(3, -1, -1):
@@ -176,12 +177,13 @@ class GanPlan(DevicePlan):
 
     def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
         s, n, B = self.store, self._name, self.B
-        local_zero = not s.owner_zeroes_grads
+        local_zero = not s.owner_zeroes_grads and not s.zero_in_before_grads
         if local_zero:
             self._zero_grads_on_side()
         self.forward()
         if local_zero:
             self._join()
+        s.before_grads()
         K.gan_loss_grad(self.logit, B, self.losses_t, self.d_disc, self.d_disc_t, self.d_gen,
                         s.grad(n("b_disc_out")) if disc else None)
         if disc:
@@ -264,13 +266,15 @@ class LstmPlan(DevicePlan):
             # no separate clear of the gradient buffer: the BPTT kernel overwrites the three small
             # gradients and zeroes the cell-kernel gradient (what the split-K GEMM below adds into)
             self.forward(train=True)
+            s.before_grads()
             K.lstm_bwd_head(s.w(n("kernel")), self.saved, s.grad(n("bias")), self.h_last, s.w_src(n("out_w")),
                             s.vec_src(n("out_b")), self.inputs["y"], s.grad(n("out_w")), s.grad(n("out_b")),
                             loss=self.losses["loss"], correct=self.correct, logits=self.logits, w_ptr=w_ptr,
                             accumulate=False, zero=s.grad(n("kernel")))
         else:
-            s.zero_grads()
             self.forward(train=True)
+            s.before_grads()
+            s.zero_grads()
             K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits,
                                 self.dlogits_t, s.grad(n("out_b")), self.correct)
             self._fork()
@@ -369,9 +373,10 @@ class ScaledLstmPlan(DevicePlan):
         s, n, mdl, B = self.store, self._name, self.model, self.B
         T, H = mdl.T, mdl.H
         TB = T * B
-        if not s.owner_zeroes_grads:
-            s.zero_grads()
         self.forward(train=True)
+        s.before_grads()
+        if not s.owner_zeroes_grads and not s.zero_in_before_grads:
+            s.zero_grads()
         K.softmax_xent_grad(self.logits, self.inputs["y"], self.losses["loss"], self.dlogits, self.dlogits_t,
                             s.grad(n("out_b")), self.correct)
         h_last = self._rows(self.Hall[-1], T - 1)

@@ -31,7 +31,7 @@ class DeviceTrainer:
                  batch: Optional[int] = None, seed: int = 0, use_graph: bool = True,
                  gan_update: str = "simultaneous", bcast: bool = True, plan_kwargs: Optional[dict] = None,
                  model_kwargs: Optional[dict] = None, partition: bool = True, timeout_s: float = 30.0,
-                 keep_grads: bool = False):
+                 keep_grads: bool = False, replicas_to_aggregate: int = 0, async_apply: str = "worker"):
         if not torch.cuda.is_available():
             raise RuntimeError("DeviceTrainer needs a CUDA device; the CPU path is psb200.session.Session")
         _lib.lib()   # fail loudly if the kernel library is missing
@@ -40,7 +40,8 @@ class DeviceTrainer:
             worker_device="/job:worker/task:%d" % rank, ps_tasks=world))
         self.model = make_model(model_name, **(model_kwargs or {})).build(self.registry)
         self.store = NvlStore(self.model, self.registry, rank, world, group, mode=mode, bcast=bcast,
-                              partition=partition, timeout_s=timeout_s, keep_grads=keep_grads)
+                              partition=partition, timeout_s=timeout_s, keep_grads=keep_grads,
+                              replicas=replicas_to_aggregate, async_apply=async_apply)
         kw = dict(plan_kwargs or {})
         if self.model.name == "gan":
             kw.setdefault("seed", seed)
@@ -52,7 +53,8 @@ class DeviceTrainer:
         self._loss_keys = list(self.plan.losses.keys())
         self._host_losses = torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory()
         # one D2H brings back the push kernel's control block: status word and global_step
-        self._host_ctrl = torch.zeros(CTRL_WORDS, dtype=torch.int32).pin_memory()
+        # (ctrl and the worker-side wctrl are adjacent in the heap: 2 x CTRL_WORDS)
+        self._host_ctrl = torch.zeros(2 * CTRL_WORDS, dtype=torch.int32).pin_memory()
         # one D2H per step for all losses: when the plan already keeps them next to each other the
         # copy reads them in place, otherwise they are gathered first
         self._dev_losses = self._adjacent_losses()
@@ -87,6 +89,9 @@ class DeviceTrainer:
         self._barrier()
         if self.use_graph and self.graph is None:
             self._capture()
+        # the ps service thread (R-of-N sync, owner-side async) starts last: after the capture, with
+        # every rank's compute copies in place
+        self.store.start_service()
 
     def _barrier(self) -> None:
         torch.cuda.synchronize()
@@ -94,7 +99,10 @@ class DeviceTrainer:
             import torch.distributed as dist
             dist.barrier(group=self.group)
 
-    def _enqueue_step(self) -> None:
+    def _enqueue_step(self, push: bool = True) -> None:
+        if not push:
+            self.plan.forward_backward()
+            return
         if self.gan_update == "alternating":
             self.plan.forward_backward(disc=True, gen=False)
             self.store.push(["train_disc"])
@@ -111,13 +119,14 @@ class DeviceTrainer:
         """One eager step on scratch state: sets kernel attributes, fills the TMA descriptor
         cache, and proves the launch sequence before it is captured."""
         before = _lib.launch_count()
-        self._enqueue_step()
-        self._launches_per_step = _lib.launch_count() - before
+        # with a decoupled ps role the push is a wait for the ps services, which are not running yet
+        self._enqueue_step(push=not self.store.decoupled)
+        self._launches_per_step = _lib.launch_count() - before + (1 if self.store.decoupled else 0)
         self._barrier()
 
     def _capture(self) -> None:
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, capture_error_mode="thread_local"):
             self._enqueue_step()
         self.graph = g
         torch.cuda.synchronize()
@@ -151,11 +160,12 @@ class DeviceTrainer:
         """The control block that holds the authoritative global_step: this rank's in sync mode
         (lock-step replicas), the step owner's in async mode."""
         gs_rank = self.store.gs_owner if self.mode == "async" else self.rank
-        return self.store.heap.tensor(self.store._ctrl_off, (CTRL_WORDS,), torch.int32, gs_rank)
+        return self.store.heap.tensor(self.store._ctrl_off, (2 * CTRL_WORDS,), torch.int32, gs_rank)
 
     def _result(self, losses: torch.Tensor, ctrl: torch.Tensor) -> Dict[str, float]:
         if self.mode == "sync" or self.store.gs_owner == self.rank:
-            self.store.check_status(int(ctrl[CTRL_STATUS]))     # a peer died / stalled: raise, do not hang
+            # a peer died / stalled: raise, do not hang
+            self.store.check_status(max(int(ctrl[CTRL_STATUS]), int(ctrl[CTRL_WORDS + CTRL_STATUS])))
         out = {k: float(losses[i]) for i, k in enumerate(self._loss_keys)}
         out["global_step"] = int(ctrl[CTRL_GLOBAL_STEP])
         return out
@@ -168,7 +178,7 @@ class DeviceTrainer:
                 "seq": 0, "stream": torch.cuda.Stream(device=dev),
                 "stage": [{k: torch.empty_like(v) for k, v in self.plan.inputs.items()} for _ in range(2)],
                 "losses": [torch.zeros(len(self._loss_keys), dtype=torch.float32).pin_memory() for _ in range(2)],
-                "gstep": [torch.zeros(CTRL_WORDS, dtype=torch.int32).pin_memory() for _ in range(2)],
+                "gstep": [torch.zeros(2 * CTRL_WORDS, dtype=torch.int32).pin_memory() for _ in range(2)],
                 "h2d": [torch.cuda.Event() for _ in range(2)], "consumed": [torch.cuda.Event() for _ in range(2)],
                 "done": [torch.cuda.Event() for _ in range(2)], "pending": [False, False],
             }

@@ -144,18 +144,22 @@ def run_worker_cpu(model_name: str, flags: Flags, cluster: ClusterSpec, server: 
 
 def run_worker_nvl(model_name: str, flags: Flags, cluster: ClusterSpec, server: Server) -> dict:
     """Worker on the NVLink transport: rank = task_index, world = number of workers; every rank
-    is also a ps shard, so ``ps_hosts`` only matters for the done-queues."""
+    is also a ps shard, so ``ps_hosts`` only matters for the done-queues.  Same Supervisor-driven
+    life cycle as the tcp transport (``encoder:147-176``): chief init/restore, non-chief wait,
+    ``while not sv.should_stop() and step < num_steps``, checkpoint timer thread, done tokens."""
+    import datetime
     import torch.distributed as dist
-    from .checkpoint import latest_checkpoint
+    from .parallel.session import NvlSession
     from .parallel.trainer import DeviceTrainer
+    from .store.nvl import PeerTimeoutError
     world = cluster.num_tasks("worker")
     rank = flags.task_index
-    if flags.sync and flags.replicas_to_aggregate not in (0, world):
-        raise SystemExit("--backend=nvl aggregates all %d replicas per step; --replicas_to_aggregate=%d "
-                         "(backup workers) needs --backend=cpu" % (world, flags.replicas_to_aggregate))
     if flags.reinit_on_join:
         raise SystemExit("--reinit_on_join reproduces a tcp-transport race (encoder:160); it has no meaning on "
                          "--backend=nvl, where all ranks initialise collectively")
+    replicas = flags.replicas_to_aggregate if flags.sync else 0
+    if replicas < 0 or replicas > world:
+        raise SystemExit("--replicas_to_aggregate must be between 1 and the number of workers (%d)" % world)
     local = int(os.environ.get("LOCAL_RANK", rank % max(1, torch.cuda.device_count())))
     torch.cuda.set_device(local)
     group = None
@@ -163,77 +167,76 @@ def run_worker_nvl(model_name: str, flags: Flags, cluster: ClusterSpec, server: 
         host, port = cluster.task_address("worker", 0).rsplit(":", 1)
         rdzv = int(os.environ.get("PSB200_RDZV_PORT", int(port) + 1))
         dist.init_process_group("gloo", init_method="tcp://%s:%d" % (host or "127.0.0.1", rdzv),
-                                rank=rank, world_size=world)
+                                rank=rank, world_size=world,
+                                timeout=datetime.timedelta(seconds=max(30.0, 4 * flags.peer_timeout_secs)))
         group = dist.group.WORLD
     tr = DeviceTrainer(model_name, rank, world, group, mode="sync" if flags.sync else "async",
                        batch=flags.batch_size or None, seed=flags.seed, gan_update=flags.gan_update,
-                       plan_kwargs={"device_noise": False} if model_name == "gan" else None)
+                       plan_kwargs={"device_noise": False} if model_name == "gan" else None,
+                       replicas_to_aggregate=replicas, async_apply=flags.async_apply,
+                       timeout_s=flags.peer_timeout_secs)
     model = tr.model
     num_steps = flags.num_steps or model.num_steps
-    is_chief = rank == 0
-    values = None
-    restored = None
-    if is_chief:
-        latest = latest_checkpoint(flags.model_dir)
-        if latest is not None:
-            values = tr.registry.initial_values(flags.seed)
-            values.update(Saver.restore(latest))
-            restored = latest
-    if world > 1:
-        box = [values]
-        dist.broadcast_object_list(box, src=0, group=group)
-        values = box[0]
-    tr.initialize(values)
-    saver = Saver(bundle_format=flags.checkpoint_format)
-    last_save = [0.0]
-
-    def maybe_checkpoint(force=False):
-        if not is_chief or not flags.save_model_secs:
-            return
-        if force or time.time() - last_save[0] >= flags.save_model_secs:
-            vals = tr.variables()
-            saver.save(vals, flags.model_dir, int(vals[model.global_step.name]))
-            last_save[0] = time.time()
-
+    sess_store = NvlSession(tr, group, is_chief=(rank == 0))
+    sv = Supervisor(is_chief=(rank == 0), logdir=flags.model_dir, store=sess_store, registry=tr.registry,
+                    model=model, saver=Saver(bundle_format=flags.checkpoint_format),
+                    save_model_secs=flags.save_model_secs, recovery_wait_secs=flags.recovery_wait_secs,
+                    seed=flags.seed, sync=False)        # sync aggregation lives in the push kernel, not in a chief thread
     mnist = read_data_sets(flags.data_dir, one_hot=True, synthetic=flags.synthetic, seed=flags.seed + rank)
     rng = np.random.RandomState(flags.seed * 7919 + rank)
     begin_time = time.time()
-    maybe_checkpoint(force=True)
-    step, local_step = 0, 0
-    pinned = {k: torch.zeros_like(v, device="cpu").pin_memory() for k, v in tr.plan.inputs.items()}
-    while step < num_steps:
-        start_time = time.time()
-        batch = _make_batch(model_name, mnist, tr.batch, rng)
-        for k, v in batch.items():
-            pinned[k].copy_(v.reshape(pinned[k].shape))
-        out = tr.step(pinned)
-        step = out["global_step"]
-        elapsed_time = time.time() - start_time
-        if local_step % max(1, flags.log_every) == 0:
-            print("Global step %d" % step, "Local step %d" % local_step,
-                  " AvgTime: %3.2fms" % float(elapsed_time * 1000), flush=True)
-        if model_name == "gan" and (step % 1000 == 0 or step == 1):
-            print('Step %i: Generator Loss: %f, Discriminator Loss: %f' % (step, out["gen_loss"], out["disc_loss"]),
-                  flush=True)
-        local_step += 1
-        maybe_checkpoint()
-    print("Total Time: %3.2fs" % float(time.time() - begin_time), flush=True)
-    result = {"local_steps": local_step, "global_step": step, "restored_from": restored}
-    if model_name == "lstm":
-        tx = torch.from_numpy(mnist.test.images[:128].reshape((-1, 28, 28))).cuda()
-        ty = torch.from_numpy(mnist.test.labels[:128]).cuda()
-        acc = tr.accuracy(tx, ty)
-        print("Test-Accuracy: %2.4f" % acc, flush=True)
-        result["test_accuracy"] = acc
-    if world > 1:
-        dist.barrier(group=group)
-    maybe_checkpoint(force=True)
-    if flags.ps_hosts:
-        store = TcpStore(cluster, tr.registry, model, num_workers=flags.workers)
-        store.enqueue_done(flags.workers)
-        store.close()
-    if world > 1:
-        dist.barrier(group=group)
+    result = {"local_steps": 0, "global_step": 0}
+    failed = None
+    with sv.managed_session():
+        step, local_step = sess_store.global_step(), 0
+        pinned = {k: torch.zeros_like(v, device="cpu").pin_memory() for k, v in tr.plan.inputs.items()}
+        try:
+            while not sv.should_stop() and step < num_steps:
+                start_time = time.time()
+                batch = _make_batch(model_name, mnist, tr.batch, rng)
+                for k, v in batch.items():
+                    pinned[k].copy_(v.reshape(pinned[k].shape))
+                out = tr.step(pinned)
+                step = out["global_step"]
+                sess_store.note_step(step)
+                elapsed_time = time.time() - start_time
+                if local_step % max(1, flags.log_every) == 0:
+                    print("Global step %d" % step, "Local step %d" % local_step,
+                          " AvgTime: %3.2fms" % float(elapsed_time * 1000), flush=True)
+                if model_name == "gan" and (step % 1000 == 0 or step == 1):
+                    print('Step %i: Generator Loss: %f, Discriminator Loss: %f' % (step, out["gen_loss"], out["disc_loss"]),
+                          flush=True)
+                local_step += 1
+        except PeerTimeoutError as e:
+            # a peer is gone or stuck: stop cleanly instead of hanging in the kernel
+            failed = str(e)
+            print("worker %d: %s -- stopping" % (rank, failed), flush=True)
+            sv.request_stop()
+        print("Total Time: %3.2fs" % float(time.time() - begin_time), flush=True)
+        result.update(local_steps=local_step, global_step=step, restored_from=sv.restored_from, failed=failed)
+        if model_name == "lstm" and failed is None:
+            tx = torch.from_numpy(mnist.test.images[:128].reshape((-1, 28, 28))).cuda()
+            ty = torch.from_numpy(mnist.test.labels[:128]).cuda()
+            acc = tr.accuracy(tx, ty)
+            print("Test-Accuracy: %2.4f" % acc, flush=True)
+            result["test_accuracy"] = acc
+        if world > 1 and failed is None:
+            try:
+                dist.barrier(group=group)          # everybody has stopped stepping: the final state is final
+            except Exception as e:                 # a dead peer must not keep the survivors here forever
+                print("worker %d: final barrier failed (%s)" % (rank, type(e).__name__), flush=True)
+        sess_store.note_step(tr.global_step() if failed is None else step)
+        sv.final_checkpoint()
+        if flags.ps_hosts:
+            store = TcpStore(cluster, tr.registry, model, num_workers=flags.workers)
+            store.enqueue_done(flags.workers)
+            store.close()
+    sv.stop()
+    if world > 1 and failed is None:
+        try:
+            dist.barrier(group=group)
+        except Exception:
+            pass
     tr.close()
     if world > 1:
         dist.destroy_process_group()

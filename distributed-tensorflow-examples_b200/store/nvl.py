@@ -37,7 +37,7 @@ class PushSeg(Structure):
                 ("eps", c_float), ("master", c_void_p), ("slot0", c_void_p), ("slot1", c_void_p),
                 ("beta_pow", c_void_p), ("w_off", c_int64), ("ld_w", c_int32), ("wt_off", c_int64),
                 ("ld_wt", c_int32), ("f_off", c_int64), ("home", c_int32), ("bcast", c_int32),
-                ("flags", c_uint32), ("nblocks", c_uint32)]
+                ("flags", c_uint32), ("nblocks", ctypes.c_uint16), ("block_x", ctypes.c_uint16)]
 
 
 class BetaUpdate(Structure):
@@ -71,6 +71,8 @@ class PeerTimeoutError(RuntimeError):
 _lib.register_signature("psb_push_apply", [POINTER(PushDesc), c_void_p])
 _lib.register_signature("psb_wait_params", [c_void_p, c_int, c_uint32, c_void_p])
 _lib.register_signature("psb_push_commit", [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_uint64, c_void_p])
+_lib.register_signature("psb_ps_service_start", [POINTER(PushDesc), c_int, POINTER(c_void_p)])
+_lib.register_signature("psb_ps_service_stop", [c_void_p, POINTER(c_uint64)])
 
 
 class _VarLayout:
@@ -86,14 +88,27 @@ class NvlStore:
 
     def __init__(self, model: Model, registry: VariableRegistry, rank: int = 0, world: int = 1,
                  group=None, mode: str = "sync", bcast: bool = True, device=None, partition: bool = True,
-                 timeout_s: float = 30.0, keep_grads: bool = False):
+                 timeout_s: float = 30.0, keep_grads: bool = False, replicas: int = 0,
+                 async_apply: str = "worker"):
         if mode not in ("sync", "async"):
             raise ValueError("mode must be 'sync' or 'async'")
+        if async_apply not in ("worker", "owner"):
+            raise ValueError("async_apply must be 'worker' (remote read-modify-write) or 'owner' (ps service)")
+        if replicas < 0 or replicas > world:
+            raise ValueError("replicas_to_aggregate must be in 1..%d" % world)
         self.model, self.registry = model, registry
         self.rank, self.world, self.group, self.mode, self.bcast = rank, world, group, mode, bcast
         self.partition = partition and world > 1
         self.timeout_ns = int(timeout_s * 1e9)
         self.keep_grads = keep_grads          # tests/debugging: leave the gradients readable after the push
+        # The ps role runs as its own native service thread (csrc/ps_service.cu) when the aggregate does
+        # not wait for everybody (sync, R < N: backup workers, stale gradients dropped) or when async
+        # updates are applied by the owner; otherwise worker and ps role share the fused push kernel.
+        self.replicas = replicas if 0 < replicas < world else 0
+        self.async_apply = async_apply if (mode == "async" and world > 1) else "worker"
+        self.decoupled = world > 1 and ((mode == "sync" and self.replicas > 0) or
+                                        (mode == "async" and self.async_apply == "owner"))
+        self._service = None
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self.layout: Dict[str, _VarLayout] = {}
         self._opt_of: Dict[str, Optimizer] = {}
@@ -107,6 +122,7 @@ class NvlStore:
         h = self.heap
         self.pad = h.tensor(self._pad_off, (self.PAD_WORDS,), torch.int32)
         self.ctrl = h.tensor(self._ctrl_off, (CTRL_WORDS,), torch.int32)
+        self.wctrl = h.tensor(self._wctrl_off, (CTRL_WORDS,), torch.int32)
         self.grads = h.tensor(self._grad_off, (self._grad_elems,), torch.float32)
         self.global_step_t = h.tensor(self._gs_off, (1,), torch.int32)
         self.gs_owner = model.global_step.ps_task % world
@@ -214,13 +230,19 @@ class NvlStore:
     def owner_zeroes_grads(self) -> bool:
         """True: the push kernel clears the accumulated gradients it has consumed (PSB_SEG_ZERO_GRAD);
         False: the plans clear the gradient buffer themselves at the start of a step."""
-        return not self.keep_grads
+        return not self.keep_grads and not self.decoupled
+
+    @property
+    def zero_in_before_grads(self) -> bool:
+        """Async with owner-side apply: the gradient buffer may only be cleared once every owner has
+        acknowledged the previous gradient, so :meth:`before_grads` does it."""
+        return self.decoupled and self.mode == "async"
 
     def _build_segs(self, owned_only: bool, peer_state: bool, kind_override: Optional[int],
                     op_names: Optional[List[str]] = None):
         """Segment table (device) + grid.x.  One segment per owned row block."""
         h = self.heap
-        segs = []
+        segs, rounds = [], []
         wanted = None
         if op_names is not None:
             wanted = {n for op in self.model.train_ops if op.name in op_names for n in op.var_list}
@@ -261,26 +283,30 @@ class NvlStore:
                 if two_d:
                     units = (((r1 - r0) + 31) // 32) * ((L.cols + 31) // 32)
                     tu = 1 if maxw >= 8 else 2
-                    s.nblocks = max(1, (units + tu - 1) // tu)
+                    rounds.append(max(1, (units + tu - 1) // tu))
                 else:
                     per_iter = 256 * 4 * (1 if maxw >= 8 else (2 if maxw >= 4 else 4))
-                    s.nblocks = max(1, (numel + per_iter - 1) // per_iter)
+                    rounds.append(max(1, (numel + per_iter - 1) // per_iter))
                 segs.append(s)
-        # s.nblocks holds the rounds of work (one round = what one block does per loop iteration).
-        # Smallest number of rounds per block R such that the whole launch fits in one wave of
-        # 2 blocks per SM: small models then finish in a single round per block.
+        # `rounds[j]` = block iterations segment j needs.  Smallest number of iterations per block R such
+        # that the whole launch fits in one wave of 2 blocks per SM: small models then finish in a single
+        # iteration per block.  The table lists every segment once per block that works on it, and the
+        # launch is one block per entry: no idle blocks, whatever the mix of segment sizes.
         budget = 296
         R = 1
-        while sum((s.nblocks + R - 1) // R for s in segs) > budget:
+        while sum((r + R - 1) // R for r in rounds) > budget:
             R += 1
-        gx = 1
-        for s in segs:
-            s.nblocks = max(1, (s.nblocks + R - 1) // R)
-            gx = max(gx, s.nblocks)
-        arr = (PushSeg * max(len(segs), 1))(*segs)
-        raw = bytes(arr) if segs else b"\0" * ctypes.sizeof(PushSeg)
+        items = []
+        for s, r in zip(segs, rounds):
+            nb = max(1, (r + R - 1) // R)
+            for x in range(nb):
+                it = PushSeg.from_buffer_copy(bytes(s))
+                it.nblocks, it.block_x = nb, x
+                items.append(it)
+        arr = (PushSeg * max(len(items), 1))(*items)
+        raw = bytes(arr) if items else b"\0" * ctypes.sizeof(PushSeg)
         dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
-        return dev, len(segs), gx
+        return dev, len(items), 1
 
     def _beta_owner(self, op_index: int) -> int:
         opt = self.model.train_ops[op_index].optimizer
@@ -369,6 +395,7 @@ class NvlStore:
         return torch.cat(parts).reshape(shape).clone()
 
     def read_all(self) -> Dict[str, torch.Tensor]:
+        self.flush()
         torch.cuda.synchronize()
         return {s.name: self.read(s.name) for s in self.registry}
 
@@ -377,11 +404,15 @@ class NvlStore:
         training stream (the checkpoint timer thread's read: like the reference's Saver it may see a
         mixture of two consecutive steps, ``encoder:138,151``).  Synchronise ``stream`` before use."""
         out = {}
+        if not hasattr(self, "_snap_bufs"):
+            self._snap_bufs = {}
         with torch.cuda.stream(stream):
             for s in self.registry:
                 off, shape, dtype, runs = self._locate(s.name)
                 n = runs[-1][1]
-                host = torch.empty(n, dtype=dtype).pin_memory()
+                host = self._snap_bufs.get(s.name)
+                if host is None:
+                    host = self._snap_bufs[s.name] = torch.empty(n, dtype=dtype).pin_memory()
                 for (e0, e1, owner) in runs:
                     host[e0:e1].copy_(self.heap.tensor(off + 4 * e0, (e1 - e0,), dtype, owner), non_blocking=True)
                 out[s.name] = host.reshape(shape)
@@ -406,12 +437,13 @@ class NvlStore:
         torch.cuda.synchronize()
 
     def global_step(self) -> int:
+        self.flush()
         r = self.gs_owner if self.mode == "async" else self.rank
         return int(self.heap.tensor(self._gs_off, (1,), torch.int32, r).item())
 
     # ------------------------------------------------------------------ failure containment
     def status(self) -> int:
-        return int(self.ctrl[CTRL_STATUS].item())
+        return max(int(self.ctrl[CTRL_STATUS].item()), int(self.wctrl[CTRL_STATUS].item()))
 
     def check_status(self, status: Optional[int] = None) -> None:
         st = self.status() if status is None else status
@@ -426,6 +458,7 @@ class NvlStore:
             self._abort_stream = torch.cuda.Stream(device=self.device)
         with torch.cuda.stream(self._abort_stream):
             self.ctrl[CTRL_ABORT:CTRL_ABORT + 1].copy_(self._abort_src, non_blocking=True)
+            self.wctrl[CTRL_ABORT:CTRL_ABORT + 1].copy_(self._abort_src, non_blocking=True)
         self._abort_stream.synchronize()
 
     # ------------------------------------------------------------------ push
@@ -468,9 +501,78 @@ class NvlStore:
         d.nbeta = nb
         return d
 
+    # ---- decoupled ps role -------------------------------------------------------------------
+    def _commit(self, wait: int) -> None:
+        _lib.check(_lib.lib().psb_push_commit(self._t_pad.data_ptr(), self.world, self.rank, self.wctrl.data_ptr(),
+                                              1 if self.mode == "async" else 0, wait, self.timeout_ns,
+                                              _lib.current_stream_ptr()), "psb_push_commit")
+
+    def before_grads(self) -> None:
+        """Called by the plans right before the first kernel that writes a gradient.  With owner-side
+        async apply the gradient buffer is still owned by the ps shards until each of them has
+        acknowledged the previous gradient: wait for that (normally long done: it overlapped the
+        forward pass), then clear what the backward kernels accumulate into."""
+        if self.zero_in_before_grads:
+            self._commit(1)
+            if self._zero_after_push:
+                self.grads.zero_()
+
+    def start_service(self, poll_us: int = 0) -> None:
+        """Start this rank's ps service thread (collective: call on every rank after the compute
+        copies are in place and after any CUDA-graph capture)."""
+        if not self.decoupled or self._service is not None:
+            return
+        sync = self.mode == "sync"
+        if "service" not in self._seg_cache:
+            self._seg_cache["service"] = self._build_segs(owned_only=True, peer_state=False, kind_override=None)
+        segs, n, gx = self._seg_cache["service"]
+        delta = sum(1 for op in self.model.train_ops if op.increments_global_step)
+        d = self._desc(segs, n, gx, True, delta, True)
+        d.phases = PH_TRY_GRADS | PH_APPLY | (PH_SIGNAL_PARAMS if sync else PH_EACH)
+        d.replicas = self.replicas if sync else 1
+        d.inv_replicas = 1.0
+        d.signal_params = 0
+        d.prof = None
+        if not sync and self.rank != self.gs_owner:
+            d.global_step = None            # one increment per gradient: only the step's owner counts
+        torch.cuda.synchronize()
+        if sync:
+            # the workers' first token is the owners' next aggregate (the parameter refresh consumed some)
+            self.wctrl[CTRL_STEP] = self.ctrl[CTRL_STEP] + 1
+        torch.cuda.synchronize()
+        if self.world > 1 and self.group is not None:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)
+        h = c_void_p()
+        _lib.check(_lib.lib().psb_ps_service_start(ctypes.byref(d), int(poll_us), ctypes.byref(h)), "psb_ps_service_start")
+        self._service = h
+        self._service_desc = d               # keeps the ctypes struct (and what it points to) alive
+
+    def stop_service(self) -> int:
+        if self._service is None:
+            return 0
+        n = c_uint64(0)
+        h, self._service = self._service, None
+        _lib.check(_lib.lib().psb_ps_service_stop(h, ctypes.byref(n)), "psb_ps_service_stop")
+        return int(n.value)
+
+    def flush(self) -> None:
+        """Async with owner-side apply: block until every owner has consumed this rank's last gradient."""
+        if self.decoupled and self.mode == "async" and self._service is not None:
+            self._commit(1)
+            torch.cuda.synchronize()
+            self.check_status()
+
     def push(self, op_names: Optional[List[str]] = None) -> None:
         """Enqueue this step's gradient push on the current stream (graph-capturable).
         ``op_names`` restricts it to some train ops (GAN alternating updates)."""
+        if self.decoupled:
+            if op_names is not None:
+                raise ValueError("per-op pushes (GAN alternating updates) need the fused push: use "
+                                 "replicas_to_aggregate == workers / async_apply='worker'")
+            self._commit(0)
+            self._push_count += 1
+            return
         stream = _lib.current_stream_ptr()
         sync = self.mode == "sync"
         key = (sync, tuple(op_names) if op_names is not None else None)
@@ -514,4 +616,5 @@ class NvlStore:
         self.grads.zero_()
 
     def close(self) -> None:
+        self.stop_service()
         self.heap.close()

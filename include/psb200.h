@@ -223,7 +223,12 @@ typedef struct psb_push_seg {
     int32_t home;           /* index into arena_ptrs that receives the copies when !bcast */
     int32_t bcast;          /* 1: write the copies into every rank's arena (push-mode all-gather) */
     uint32_t flags;         /* PSB_SEG_* */
-    uint32_t nblocks;       /* blocks of the launch (of grid.x) that share this segment; 0 = all */
+    uint16_t nblocks;       /* blocks that share this segment's work (block k of them takes units k, k+nblocks,
+                               ...); 0 = grid.x */
+    uint16_t block_x;       /* this entry is for block block_x + blockIdx.x of those.  A caller may list a
+                               segment once (block_x = 0) and launch grid.x = blocks_per_seg blocks per entry, or
+                               list it nblocks times with block_x = 0..nblocks-1 and launch ONE block per entry:
+                               segments of very different sizes then share one wave without idle blocks */
 } psb_push_seg_t;
 /* After reading them, overwrite this segment's gradients with zero in EVERY rank's gradient
  * buffer, so producers that accumulate (bias column sums, split-K partial sums) need no separate
@@ -327,6 +332,15 @@ int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
  * ref: token_queue dequeue / accumulator apply_grad of SyncReplicasOptimizer; plain minimize(). */
 int psb_push_commit(uint32_t* const* pad_ptrs, int world, int rank, uint32_t* worker_ctrl,
                     int async_mode, int wait, uint64_t timeout_ns, void* stream);
+/* The ps role of this rank as a native service thread (csrc/ps_service.cu): a std::thread with its
+ * own high-priority stream launches psb_push_apply(desc) over and over; `desc->phases` must be
+ * the non-blocking form (PSB_PUSH_TRY_GRADS | PSB_PUSH_APPLY | PSB_PUSH_SIGNAL_PARAMS, plus
+ * PSB_PUSH_EACH for async), so no kernel of the service ever waits for anybody.  The shard keeps
+ * serving its peers whatever this rank's worker thread does.  `desc` is copied; the device memory
+ * it points to must outlive the service.  poll_us > 0 sleeps between launches.
+ * ref: the worker service of a ps task, encoder:96-109; Apply* running on the ps, encoder:137. */
+int psb_ps_service_start(const psb_push_desc_t* desc, int poll_us, void** handle);
+int psb_ps_service_stop(void* handle, uint64_t* launches /* optional out */);
 /* Block the stream until every rank has published params-ready >= step_id on `pad`. */
 int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream);
 

@@ -18,7 +18,7 @@ def _free_port():
     return p
 
 
-def _run(n, *args, timeout=300):
+def _run(n, *args, timeout=180):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n),
            "--master-addr", "127.0.0.1", "--master-port", str(_free_port()),
            os.path.join(ROOT, "tests", "multigpu_worker.py")] + list(args)
@@ -48,6 +48,26 @@ def test_signal_protocol_under_host_jitter(model):
     """T4 stress: random per-rank host stalls and a mix of blocking / pipelined submissions must not
     change a single bit of the sync-mode result (device-side step tokens order everything)."""
     _run(2, "--model", model, "--mode", "sync", "--stress", "60")
+
+
+@pytest.mark.parametrize("model", ["lstm", "encoder"])
+def test_sync_r_of_n_keeps_stepping_past_a_slow_rank(model):
+    """--replicas_to_aggregate < workers on the NVLink transport: ps service thread per
+    rank, first-R aggregation, stale gradients dropped, tokens."""
+    _run(2, "--model", model, "--mode", "sync", "--replicas", "1", "--slow_rank", "1", "--steps", "40")
+
+
+@pytest.mark.parametrize("model", ["lstm", "gan"])
+def test_async_owner_side_apply_counts_every_update(model):
+    _run(2, "--model", model, "--mode", "async", "--async_apply", "owner", "--steps", "20")
+
+
+def test_stalled_peer_raises_instead_of_hanging():
+    _run(2, "--model", "lstm", "--mode", "sync", "--stall", "1")
+
+
+def test_noalloc_entry_point_across_ranks():
+    _run(2, "--model", "lstm", "--mode", "sync", "--noalloc", "1")
 
 
 def test_nvl_entrypoints_through_the_reference_cli(tmp_path):

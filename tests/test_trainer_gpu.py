@@ -181,7 +181,7 @@ def test_scaled_stacked_lstm_matches_oracle(fuse_fwd):
     from psb200.parallel.trainer import DeviceTrainer
     dims = dict(num_input=64, timesteps=6, num_hidden=128, num_layers=2, num_classes=10, lr=0.5)
     tr = DeviceTrainer("scaled_lstm", use_graph=True, seed=4, batch=64, model_kwargs=dims,
-                       plan_kwargs={"fuse_fwd": fuse_fwd})
+                       plan_kwargs={"fuse_fwd": fuse_fwd}, keep_grads=True)
     try:
         values = tr.registry.initial_values(4)
         for s in tr.registry.trainable():
