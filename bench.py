@@ -163,7 +163,8 @@ def run_psb200(args):
         dims = dict(num_input=args.hidden, timesteps=args.seq, num_hidden=args.hidden, num_layers=args.layers)
     tr = DeviceTrainer(model, rank, world, group, mode=args.mode, seed=args.seed, batch=B,
                        gan_update=args.gan_update, plan_kwargs=kw, model_kwargs=dims, bcast=bool(args.bcast),
-                       partition=bool(args.partition))
+                       partition=bool(args.partition), replicas_to_aggregate=args.replicas,
+                       async_apply=args.async_apply)
     tr.initialize()
     batches = synthetic_batches(model, B, 2 if model == "scaled_lstm" else 8, args.seed * 1000 + rank, dims)
     dev_batches = [{k: v.cuda() for k, v in b.items()} for b in batches]
@@ -240,7 +241,11 @@ def run_psb200(args):
             "impl": "psb200",
             "config": {"model": MODEL_LABEL[model] if dims is None else "scaled %d-layer LSTM hidden %d seq %d bf16, SGD" % (args.layers, args.hidden, args.seq),
                        "global_batch": B * world, "seq_len": 28 if model == "lstm" else (args.seq if dims else None),
-                       "parallelism": "dp%d ps-sharded (%s%s)" % (world, args.mode, "" if args.bcast else ", pull-fused"),
+                       "parallelism": "dp%d ps-sharded (%s%s%s%s)" % (
+                           world, args.mode, "" if args.bcast else ", pull-fused",
+                           ", R=%d of %d via ps service" % (args.replicas, world) if 0 < args.replicas < world else "",
+                           ", owner-side apply via ps service" if args.mode == "async" and args.async_apply == "owner" and world > 1 else ""),
+                       "gan_update": args.gan_update if model == "gan" else None,
                        "l2": "flushed between timed iterations (256 MiB write outside the event pairs)",
                        "cuda_graph": used_graph,
                        "baseline_for_vs": base_label},
@@ -308,18 +313,31 @@ def main():
     ap.add_argument("--impl", default="psb200", choices=["psb200", "reference", "torch_ddp", "torch_ddp_graph"])
     ap.add_argument("--baseline", type=int, default=1, help="1: also run the CUDA-graphed PyTorch baseline in this invocation")
     ap.add_argument("--partition", type=int, default=1, help="1: big variables are split in row blocks over all ranks")
+    ap.add_argument("--replicas", type=int, default=0, help="sync: aggregate the first R < N gradients (ps service thread)")
+    ap.add_argument("--async_apply", default="worker", choices=["worker", "owner"],
+                    help="async: who applies a gradient -- the pushing worker (remote RMW) or the owner's ps service")
     ap.add_argument("--bcast", type=int, default=1, help="1: push kernel refreshes every rank's arena; 0: consumers pull from the owner")
     ap.add_argument("--seed", type=int, default=0)
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
+    # stdout carries exactly ONE line, the JSON: anything libraries print there (NCCL's version
+    # banner, warnings) is sent to stderr for the duration of the run
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(obj):
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(obj) + "\n").encode())
+
     if args.impl == "reference":
         if int(os.environ.get("RANK", "0")) == 0:
-            print(json.dumps(run_reference(args)), flush=True)
+            emit(run_reference(args))
         return
     res = run_psb200(args) if args.impl == "psb200" else run_torch_ddp(args)
     if res is not None:
-        print(json.dumps(res), flush=True)
+        emit(res)
 
 
 if __name__ == "__main__":

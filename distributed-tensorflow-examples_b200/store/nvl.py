@@ -547,6 +547,8 @@ class NvlStore:
         _lib.check(_lib.lib().psb_ps_service_start(ctypes.byref(d), int(poll_us), ctypes.byref(h)), "psb_ps_service_start")
         self._service = h
         self._service_desc = d               # keeps the ctypes struct (and what it points to) alive
+        import atexit
+        atexit.register(self.stop_service)   # never leave the native thread running into interpreter teardown
 
     def stop_service(self) -> int:
         if self._service is None:
