@@ -39,6 +39,17 @@ struct EpiArgs {
     int atomic_f32;      // split-K: partial sums are atomically added into out_f32 (caller zeroes it)
     long long split_stride;   // split-K: CTA z stores its partial at out_f32 + z*split_stride instead (deterministic)
     int b_static;             // B was NOT written by the preceding kernel: its first stages may be fetched before griddepcontrol.wait
+    // ---- parameter pull with per-block readiness: B is a weight copy that the owners' push kernels
+    // are refreshing row block by row block; a tile is fetched as soon as ITS block's flag shows this step
+    const uint32_t* ready;    // flag words, one per row block of the variable behind B (nullptr = no flags)
+    const uint32_t* ready_step;   // device word holding the step the flags must reach
+    int ready_rows;           // variable rows per block
+    int ready_dim;            // 0: the blocks partition K (B = W^T copy), 1: they partition N (B = W copy)
+    int ready_nblk;
+    int ready_first;          // dim 0: k-blocks are visited starting at this row block (own block first, fixed per rank)
+    const uint32_t* bias_ready;   // flag word of the bias variable (nullptr = none)
+    uint32_t* ready_status;   // set to PSB_PUSH_ST_TIMEOUT_PARAMS when a wait gives up
+    unsigned long long ready_timeout_ns;
     // ---- fused large-H LSTM step (BN == 128 only): B tile = 4 gate blocks x 32 units gathered with four
     // 32-row TMA boxes, epilogue = the BasicLSTMCell pointwise.  Active when lstm_c != nullptr.
     const float* lstm_gx;     // fp32 [B, 4H] x-part pre-activations of this timestep
@@ -231,6 +242,26 @@ __device__ __forceinline__ void lstm_step_epilogue(const EpiArgs& e, uint32_t t_
     }
 }
 
+// Block until the owner of row block `blk` has published this step's copy of it.  One thread.
+__device__ __forceinline__ void wait_block_ready(const EpiArgs& e, const uint32_t* flag, uint32_t want) {
+    unsigned long long t0 = 0;
+    uint32_t it = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(flag) - want) < 0) {
+        if ((++it & 1023u) == 0 && e.ready_timeout_ns != 0) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > e.ready_timeout_ns) {
+                if (e.ready_status != nullptr) atomicMax(e.ready_status, 2u);   // PSB_PUSH_ST_TIMEOUT_PARAMS
+                return;
+            }
+        }
+    }
+    // what the flag guards was written through the generic proxy (by another GPU); TMA reads it
+    // through the async proxy
+    asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
 template <int BN, bool kPullB>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
@@ -306,17 +337,42 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             if (lane == 0) {
                 int s = 0;
                 uint32_t ph = 0;
+                // pull with readiness flags: visit the k-blocks in a rotated order that starts with this
+                // rank's own row block (refreshed first, by the push kernel that just ran here) and wait for
+                // each block's flag right before its first tile is requested -- the tensor cores work on the
+                // blocks that have arrived while the others are still in flight over NVLink
+                const bool flags = epi.ready != nullptr;
+                uint32_t want = 0;
+                int rot = 0;
+                if (flags) {
+                    want = *reinterpret_cast<const volatile uint32_t*>(epi.ready_step);
+                    if (epi.ready_dim == 0) {
+                        if (gridDim.z == 1) rot = (epi.ready_first * epi.ready_rows) / kBK;
+                    } else {
+                        const int nlast = (n0 + BN < N ? n0 + BN : N) - 1;
+                        for (int b = n0 / epi.ready_rows; b <= nlast / epi.ready_rows && b < epi.ready_nblk; ++b)
+                            wait_block_ready(epi, epi.ready + b, want);
+                    }
+                }
+                int waited = -1;
                 for (int kb = kb0; kb < kb1; ++kb) {
+                    int kbr = kb;
+                    if (rot != 0) { kbr = kb + rot; if (kbr >= kb1) kbr -= (kb1 - kb0); }
                     uint8_t* a_dst = smem + s * kStage;
                     uint8_t* b_dst = a_dst + kBM * 128;
+                    if (flags && epi.ready_dim == 0) {
+                        const int klast = (kbr * kBK + kBK < K ? kbr * kBK + kBK : K) - 1;
+                        for (int b = (kbr * kBK) / epi.ready_rows; b <= klast / epi.ready_rows && b < epi.ready_nblk; ++b)
+                            if (b != waited) { wait_block_ready(epi, epi.ready + b, want); waited = b; }
+                    }
                     if (kb - kb0 < pre) {
                         // B of this stage is already in flight (and its expect_tx armed)
-                        tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
+                        tma_load_2d(a_dst, &tma_a, &full_bar[s], kbr * kBK, m0);
                     } else {
                         mbar_wait(&empty_bar[s], ph ^ 1);
                         mbar_expect_tx(&full_bar[s], kStage);
-                        tma_load_2d(a_dst, &tma_a, &full_bar[s], kb * kBK, m0);
-                        load_b(b_dst, &full_bar[s], kb * kBK);
+                        tma_load_2d(a_dst, &tma_a, &full_bar[s], kbr * kBK, m0);
+                        load_b(b_dst, &full_bar[s], kbr * kBK);
                     }
                     if (++s == stages) { s = 0; ph ^= 1; }
                 }
@@ -385,6 +441,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         }
     } else {
         // ===================== epilogue =====================
+        if (epi.bias_ready != nullptr) {
+            // the bias vector is being refreshed by its owner too
+            if (lane == 0) wait_block_ready(epi, epi.bias_ready, *reinterpret_cast<const volatile uint32_t*>(epi.ready_step));
+            __syncwarp();
+        }
         mbar_wait(&tmem_full_bar, 0);
         tc_fence_after_sync();
         const uint32_t quad = warp & 3;       // TMEM lane quadrant this warp may read
@@ -491,7 +552,10 @@ static int gemm_entry(const void* A, int lda, const void* B, int ldb, int M, int
     }
     const CUtensorMap* ta = tensor_map_bf16_2d(A, M, K, lda, kBM);
     if (!ta) return PSB_ERR_DRIVER;
-    const CUtensorMap* tb = ta;      // unused by the pull variant
+    // pull_mode 0 (default): the peer copy is read by TMA like a local one -- a tensor map over the
+    // peer-mapped address; pull_mode 1: the producer warp's 128-bit ld.global variant
+    if (pull && epi->pull_mode == 0) pull = false;
+    const CUtensorMap* tb = ta;      // unused by the ld.global pull variant
     if (!pull) {
         tb = tensor_map_bf16_2d(B, N, K, ldb, bn);
         if (!tb) return PSB_ERR_DRIVER;
@@ -514,6 +578,16 @@ static int gemm_entry(const void* A, int lda, const void* B, int ldb, int M, int
     e.atomic_f32 = 0;
     e.split_stride = 0;
     e.b_static = epi->b_static;
+    e.ready = epi->ready; e.ready_step = epi->ready_step; e.ready_rows = epi->ready_rows; e.ready_dim = epi->ready_dim;
+    e.ready_nblk = epi->ready_nblk; e.ready_first = epi->ready_first; e.bias_ready = epi->bias_ready;
+    e.ready_status = epi->ready_status; e.ready_timeout_ns = epi->ready_timeout_ns;
+    if (e.ready != nullptr || e.bias_ready != nullptr) {
+        if (!e.ready_step) return fail(PSB_ERR_ARG, "%s: readiness flags need ready_step", who);
+        if (e.ready != nullptr && (e.ready_rows < 1 || e.ready_nblk < 1 || e.ready_first < 0 || e.ready_first >= e.ready_nblk))
+            return fail(PSB_ERR_ARG, "%s: bad readiness geometry", who);
+        if (pull) return fail(PSB_ERR_ARG, "%s: readiness flags go with the TMA pull (pull_mode 0)", who);
+        e.b_static = 0;          // B is exactly what is NOT static
+    }
     e.lstm_gx = nullptr; e.ld_gx = 0; e.lstm_bias = nullptr; e.forget_bias = 0.f; e.lstm_c = nullptr; e.lstm_h = nullptr;
     e.ld_lstm_h = 0; e.lstm_gates = nullptr; e.lstm_csave = nullptr; e.lstm_H = 0;
     // split-K for skinny problems with a long reduction (e.g. dh = dG Wh^T of the large-H LSTM:

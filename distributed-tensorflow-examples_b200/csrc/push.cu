@@ -83,6 +83,8 @@ struct PushArgs {
     int replicas;                      // gradients to aggregate (R of N); <= 0 or >= world: all
     unsigned long long* prof;          // optional [8]: t0, t1, -, -, sum(wait grads), sum(apply), sum(wait params), calls
     unsigned long long timeout_ns;     // 0 = wait forever
+    uint32_t* const* ready_ptrs;       // [world] readiness arrays (per-segment "this row block is refreshed" flags)
+    uint32_t* seg_done;                // finished-block counters, one per readiness word
 };
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -224,6 +226,7 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
     __shared__ int s_bad;
     __shared__ uint32_t s_mask;
     __shared__ bool is_last;
+    __shared__ bool seg_last;
     __shared__ __nv_bfloat16 tile[2][32][34];
 
     const int tid = threadIdx.x;
@@ -532,10 +535,21 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
     if (tid == 0) {
         if (bad_grads) atomicMax(ctrl + kCtrlStatus, static_cast<uint32_t>(bad_grads));
         release_fence(peers);
+        seg_last = false;
+        if (has_work && go && s.ready_slot != 0 && a.ready_ptrs != nullptr) {
+            // last block of this segment: its row block is complete in every arena it goes to
+            uint32_t* cnt = a.seg_done + (s.ready_slot - 1);
+            if (atomicAdd(cnt, 1u) == nb - 1) {
+                *cnt = 0;
+                __threadfence();
+                seg_last = true;
+            }
+        }
         const uint32_t prev = atomicAdd(ctrl + kCtrlDone, 1u);
         is_last = (prev == total_blocks - 1);
     }
     __syncthreads();
+    if (seg_last && tid < a.world) st_release_sys(a.ready_ptrs[tid] + (s.ready_slot - 1), a.step_id);
     unsigned long long t_applied = 0;
     if (is_last) {
         const bool failed = ld_volatile_u32(ctrl + kCtrlStatus) != 0;
@@ -660,6 +674,16 @@ __global__ void wait_params_kernel(uint32_t* pad, int world, uint32_t step_id) {
     }
 }
 
+// The same against the token this rank's last push recorded, bounded.
+__global__ void wait_params_token_kernel(uint32_t* pad, int world, uint32_t* ctrl, unsigned long long timeout_ns) {
+    const Spin sp{ctrl + kCtrlAbort, timeout_ns};
+    const uint32_t step = ld_volatile_u32(ctrl + kCtrlStep);
+    if (static_cast<int>(threadIdx.x) < world) {
+        const int bad = spin_flag(pad + kPadParams + threadIdx.x, step, sp, PSB_PUSH_ST_TIMEOUT_PARAMS);
+        if (bad) atomicMax(ctrl + kCtrlStatus, static_cast<uint32_t>(bad));
+    }
+}
+
 static int check_desc(const psb_push_desc_t* d, const char* who, bool device_tables) {
     if (!d) return fail(PSB_ERR_ARG, "%s: null descriptor", who);
     if (d->world < 1 || d->world > kMaxWorld || d->rank < 0 || d->rank >= d->world)
@@ -693,6 +717,8 @@ static void fill_args(PushArgs& a, const psb_push_desc_t* d) {
     a.replicas = d->replicas;
     a.prof = reinterpret_cast<unsigned long long*>(d->prof);
     a.timeout_ns = d->timeout_ns;
+    a.ready_ptrs = d->seg_done != nullptr ? d->ready_ptrs : nullptr;
+    a.seg_done = d->seg_done;
 }
 
 static int launch_push(const PushArgs& a, dim3 grid, cudaStream_t st, bool pdl) {
@@ -748,6 +774,13 @@ extern "C" int psb_push_commit(uint32_t* const* pad_ptrs, int world, int rank, u
     return after_launch("push_commit");
 }
 
+extern "C" int psb_wait_params_token(uint32_t* pad, int world, uint32_t* local_ctrl, uint64_t timeout_ns, void* stream) {
+    using namespace psb;
+    if (!pad || !local_ctrl || world < 1 || world > 16) return fail(PSB_ERR_ARG, "psb_wait_params_token: bad argument");
+    wait_params_token_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(pad, world, local_ctrl, timeout_ns);
+    return after_launch("wait_params_token");
+}
+
 extern "C" int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream) {
     using namespace psb;
     if (!pad || world < 1 || world > 16) return fail(PSB_ERR_ARG, "psb_wait_params: bad argument");
@@ -766,7 +799,7 @@ extern "C" int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void*
 // start-up, or code on a latency path where an allocation (an implicit device
 // synchronisation) is not acceptable.  For them this entry point keeps all of that in ONE
 // file-scope device array of fixed size, so the library's own image provides the memory:
-// every GPU that loads this library holds sizeof(NoAllocScratch) = 8960 bytes (8.75 KiB)
+// every GPU that loads this library holds sizeof(NoAllocScratch) = 9472 bytes (9.25 KiB)
 // until the process exits, whether or not this entry point is ever called.
 //
 // What the caller must know
@@ -801,7 +834,7 @@ struct NoAllocScratch {
     float* farena_ptrs[PSB_NOALLOC_MAX_WORLD];
     uint32_t* pad_ptrs[PSB_NOALLOC_MAX_WORLD];
 };
-static_assert(sizeof(NoAllocScratch) == 8960, "update the size quoted in psb200.h, DESIGN.md and INTEGRATION.md");
+static_assert(sizeof(NoAllocScratch) == 9472, "update the size quoted in psb200.h, DESIGN.md and INTEGRATION.md");
 
 // In host code this name is only a handle for cudaGetSymbolAddress; the device address it
 // resolves to is what gets passed to the kernel.

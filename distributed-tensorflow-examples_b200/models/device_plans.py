@@ -94,9 +94,9 @@ class EncoderPlan(DevicePlan):
         s, n = self.store, self._name
         K.cast_transpose(self.inputs["x"], self.act[0], self.act_t[0] if need_t else None, clear=clear)
         for l in range(3):
-            K.gemm(self.act[l], s.wt_src(n(self.wkeys[l])), bias=s.vec_src(n(self.bkeys[l])), act=ACT_SIGMOID,
+            K.gemm(self.act[l], s.wt_src(n(self.wkeys[l])), bias=s.vec_src(n(self.bkeys[l])), bias_ready=s.ready_for(n(self.bkeys[l])), act=ACT_SIGMOID,
                    out=self.act[l + 1], out_t=self.act_t[l + 1] if need_t else None, b_static=True)
-        K.gemm(self.act[3], s.wt_src(n(self.wkeys[3])), bias=s.vec_src(n(self.bkeys[3])), act=ACT_SIGMOID,
+        K.gemm(self.act[3], s.wt_src(n(self.wkeys[3])), bias=s.vec_src(n(self.bkeys[3])), bias_ready=s.ready_for(n(self.bkeys[3])), act=ACT_SIGMOID,
                out_f32=self.y, b_static=True)
 
     def forward_backward(self) -> None:
@@ -166,13 +166,13 @@ class GanPlan(DevicePlan):
                             self.noise_counter, out=self.inputs["z"], out_bf16=self.Z, out_t=self.ZT)
         else:
             K.cast_transpose(self.inputs["z"], self.Z, self.ZT)
-        K.gemm(self.Z, s.wt_src(n("w_gen_hidden1")), bias=s.vec_src(n("b_gen_hidden1")), act=ACT_RELU,
+        K.gemm(self.Z, s.wt_src(n("w_gen_hidden1")), bias=s.vec_src(n("b_gen_hidden1")), bias_ready=s.ready_for(n("b_gen_hidden1")), act=ACT_RELU,
                out=self.GH, out_t=self.GHT, b_static=True)
-        K.gemm(self.GH, s.wt_src(n("w_gen_out")), bias=s.vec_src(n("b_gen_out")), act=ACT_SIGMOID,
+        K.gemm(self.GH, s.wt_src(n("w_gen_out")), bias=s.vec_src(n("b_gen_out")), bias_ready=s.ready_for(n("b_gen_out")), act=ACT_SIGMOID,
                out=self.Din_fake, out_t=self.DinT_fake, b_static=True)
-        K.gemm(self.Din, s.wt_src(n("w_disc_hidden1")), bias=s.vec_src(n("b_disc_hidden1")), act=ACT_RELU,
+        K.gemm(self.Din, s.wt_src(n("w_disc_hidden1")), bias=s.vec_src(n("b_disc_hidden1")), bias_ready=s.ready_for(n("b_disc_hidden1")), act=ACT_RELU,
                out=self.DH, out_t=self.DHT, b_static=True)
-        K.gemm(self.DH, s.wt_src(n("w_disc_out")), bias=s.vec_src(n("b_disc_out")), act=ACT_NONE,
+        K.gemm(self.DH, s.wt_src(n("w_disc_out")), bias=s.vec_src(n("b_disc_out")), bias_ready=s.ready_for(n("b_disc_out")), act=ACT_NONE,
                out_f32=self.logit, b_static=True)
 
     def forward_backward(self, disc: bool = True, gen: bool = True) -> None:
@@ -245,12 +245,13 @@ class LstmPlan(DevicePlan):
 
     def forward(self, train: bool = False) -> None:
         s, n = self.store, self._name
+        s.wait_all_params()          # pull mode: the LSTM kernels read the owner's copies without flags
         wt_ptr, _ = self._kernel_ptrs()
         K.lstm_fwd(self.inputs["x"], s.wt(n("kernel")), s.vec_src(n("bias")), lstm_mod.forget_bias,
                    self.h_last, self.h_last_t if train else None, self.saved if train else None,
                    wt_ptr=wt_ptr)
         if not (train and self.fuse_head):
-            K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits, b_static=True)
+            K.gemm(self.h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), bias_ready=s.ready_for(n("out_b")), out_f32=self.logits, b_static=True)
 
     def evaluate(self) -> None:
         """Fills ``losses['loss']`` and ``correct`` for the current inputs without touching
@@ -344,6 +345,7 @@ class ScaledLstmPlan(DevicePlan):
     def forward(self, train: bool = True) -> None:
         s, n, mdl, B = self.store, self._name, self.model, self.B
         T, H = mdl.T, mdl.H
+        s.wait_all_params()          # pull mode: column views of the kernels carry no readiness flags
         K.cast_transpose(self.inputs["x"].view(T * B, mdl.I), self.X0, self.X0T if train else None)
         inp = self.X0
         for l in range(mdl.L):
@@ -367,7 +369,7 @@ class ScaledLstmPlan(DevicePlan):
                                 self.c_all[l][t * B:(t + 1) * B] if train else None)
             inp = self.Hall[l]
         h_last = self._rows(self.Hall[-1], T - 1)
-        K.gemm(h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), out_f32=self.logits, b_static=True)
+        K.gemm(h_last, s.wt_src(n("out_w")), bias=s.vec_src(n("out_b")), bias_ready=s.ready_for(n("out_b")), out_f32=self.logits, b_static=True)
 
     def forward_backward(self) -> None:
         s, n, mdl, B = self.store, self._name, self.model, self.B

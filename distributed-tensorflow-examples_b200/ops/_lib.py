@@ -25,6 +25,9 @@ class Epilogue(Structure):
         ("out_t", c_void_p), ("ld_out_t", c_int),
         ("out_f32", c_void_p), ("ld_f32", c_int),
         ("colsum", c_void_p), ("split_k", c_int), ("split_stride", ctypes.c_longlong), ("b_static", c_int),
+        ("ready", c_void_p), ("ready_step", c_void_p), ("ready_rows", c_int), ("ready_dim", c_int),
+        ("ready_nblk", c_int), ("ready_first", c_int), ("bias_ready", c_void_p), ("ready_status", c_void_p),
+        ("ready_timeout_ns", c_uint64), ("pull_mode", c_int),
     ]
 
 

@@ -28,11 +28,12 @@ class BMat:
     next GEMM (TMA needs 16-byte row strides: K=100 -> 104, K=156 -> 160, N=1 -> 8).
     """
 
-    __slots__ = ("t", "rows", "cols", "remote")
+    __slots__ = ("t", "rows", "cols", "remote", "ready")
 
     def __init__(self, rows: int, cols: int, device="cuda", data: Optional[torch.Tensor] = None):
         self.rows, self.cols = int(rows), int(cols)
         self.remote = False          # True: the storage is another GPU's memory (peer mapping)
+        self.ready = None            # readiness flags of the variable behind this copy (store/nvl.py: ReadyInfo)
         self.t = torch.zeros(self.rows, round_up(self.cols, 8), dtype=torch.bfloat16, device=device)
         if data is not None:
             self.t[:, : self.cols].copy_(data)
@@ -44,7 +45,7 @@ class BMat:
     def rows_view(self, r0: int, r1: int) -> "BMat":
         """Rows ``r0:r1`` as a matrix sharing this storage."""
         m = BMat.__new__(BMat)
-        m.rows, m.cols, m.t, m.remote = r1 - r0, self.cols, self.t[r0:r1], self.remote
+        m.rows, m.cols, m.t, m.remote, m.ready = r1 - r0, self.cols, self.t[r0:r1], self.remote, None
         return m
 
     def cols_view(self, c0: int, c1: int) -> "BMat":
@@ -52,7 +53,7 @@ class BMat:
         if c0 % 8:
             raise ValueError("column views must start on a 16-byte boundary")
         m = BMat.__new__(BMat)
-        m.rows, m.cols, m.t, m.remote = self.rows, c1 - c0, self.t[:, c0:], self.remote
+        m.rows, m.cols, m.t, m.remote, m.ready = self.rows, c1 - c0, self.t[:, c0:], self.remote, None
         return m
 
     @property
@@ -65,7 +66,7 @@ class BMat:
     @staticmethod
     def wrap(t: torch.Tensor, rows: int, cols: int, remote: bool = False) -> "BMat":
         m = BMat.__new__(BMat)
-        m.rows, m.cols, m.t, m.remote = rows, cols, t, remote
+        m.rows, m.cols, m.t, m.remote, m.ready = rows, cols, t, remote, None
         return m
 
     @staticmethod
@@ -86,7 +87,7 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
          out: Optional[BMat] = None, out_t: Optional[BMat] = None,
          out_f32: Optional[torch.Tensor] = None, colsum: Optional[torch.Tensor] = None,
          block_n: int = 0, k: Optional[int] = None, split_k: int = 1, split_stride: int = 0,
-         b_static: bool = False) -> None:
+         b_static: bool = False, bias_ready=None, pull_mode: int = 0) -> None:
     """``acc = alpha * a @ b.T`` (a: [M,K], b: [N,K]) with the fused epilogue of
     ``psb_gemm_bf16``.  ``k`` overrides the reduction length (defaults to ``a.cols``).
     ``b_static=True`` promises that ``b`` (a weight copy) was not written by the kernel launched
@@ -113,6 +114,16 @@ def gemm(a: BMat, b: BMat, *, alpha: float = 1.0, bias: Optional[torch.Tensor] =
     e.split_k = int(split_k)
     e.split_stride = int(split_stride)
     e.b_static = 1 if b_static else 0
+    e.pull_mode = int(pull_mode)
+    rd = getattr(b, "ready", None)
+    if rd is not None:
+        # the copy is refreshed row block by row block by the owners' push kernels: gate the tiles on
+        # their flags (parameter pull fused into this GEMM, overlapped tile by tile)
+        e.ready, e.ready_step, e.ready_rows, e.ready_dim = rd.flags, rd.step, rd.rows, rd.dim
+        e.ready_nblk, e.ready_first, e.ready_status, e.ready_timeout_ns = rd.nblk, rd.first, rd.status, rd.timeout_ns
+    if bias_ready is not None:
+        e.bias_ready, e.ready_step = bias_ready.flags, bias_ready.step
+        e.ready_status, e.ready_timeout_ns = bias_ready.status, bias_ready.timeout_ns
     if out is not None and (out.rows != M or out.cols != N):
         raise ValueError("gemm: out must be [%d,%d]" % (M, N))
     if out_t is not None and (out_t.rows != N or out_t.cols != M):

@@ -37,7 +37,8 @@ class PushSeg(Structure):
                 ("eps", c_float), ("master", c_void_p), ("slot0", c_void_p), ("slot1", c_void_p),
                 ("beta_pow", c_void_p), ("w_off", c_int64), ("ld_w", c_int32), ("wt_off", c_int64),
                 ("ld_wt", c_int32), ("f_off", c_int64), ("home", c_int32), ("bcast", c_int32),
-                ("flags", c_uint32), ("nblocks", ctypes.c_uint16), ("block_x", ctypes.c_uint16)]
+                ("flags", c_uint32), ("nblocks", ctypes.c_uint16), ("block_x", ctypes.c_uint16),
+                ("ready_slot", c_uint32), ("reserved_", c_uint32)]
 
 
 class BetaUpdate(Structure):
@@ -51,7 +52,8 @@ class PushDesc(Structure):
                 ("local_ctrl", c_void_p), ("beta", BetaUpdate * 2), ("nbeta", c_int),
                 ("global_step", c_void_p), ("step_delta", c_int), ("async_sgd_atomic", c_int),
                 ("signal_params", c_int), ("blocks_per_seg", c_int), ("prof", c_void_p),
-                ("phases", c_int), ("replicas", c_int), ("timeout_ns", c_uint64)]
+                ("phases", c_int), ("replicas", c_int), ("timeout_ns", c_uint64),
+                ("ready_ptrs", c_void_p), ("seg_done", c_void_p)]
 
 
 SEG_ZERO_GRAD = 1
@@ -63,6 +65,15 @@ STATUS_TEXT = {1: "timed out waiting for a peer's gradients", 2: "timed out wait
                3: "aborted by the host"}
 
 
+class ReadyInfo:
+    """Readiness flags of one variable as a consuming GEMM needs them (``psb_epilogue_t.ready*``)."""
+    __slots__ = ("flags", "step", "rows", "dim", "nblk", "first", "status", "timeout_ns")
+
+    def __init__(self, flags, step, rows, dim, nblk, first, status, timeout_ns):
+        self.flags, self.step, self.rows, self.dim, self.nblk = flags, step, rows, dim, nblk
+        self.first, self.status, self.timeout_ns = first, status, timeout_ns
+
+
 class PeerTimeoutError(RuntimeError):
     """A cross-GPU wait inside the push kernel ended on its deadline or on the abort word: a peer
     rank is dead or stuck.  The step was not applied on this rank."""
@@ -71,13 +82,14 @@ class PeerTimeoutError(RuntimeError):
 _lib.register_signature("psb_push_apply", [POINTER(PushDesc), c_void_p])
 _lib.register_signature("psb_wait_params", [c_void_p, c_int, c_uint32, c_void_p])
 _lib.register_signature("psb_push_commit", [c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_uint64, c_void_p])
+_lib.register_signature("psb_wait_params_token", [c_void_p, c_int, c_void_p, c_uint64, c_void_p])
 _lib.register_signature("psb_ps_service_start", [POINTER(PushDesc), c_int, POINTER(c_void_p)])
 _lib.register_signature("psb_ps_service_stop", [c_void_p, POINTER(c_uint64)])
 
 
 class _VarLayout:
     __slots__ = ("spec", "rows", "cols", "grad_off", "master_off", "slot_offs", "w_off", "ld_w",
-                 "wt_off", "ld_wt", "f_off", "owner", "blocks")
+                 "wt_off", "ld_wt", "f_off", "owner", "blocks", "ready_base")
 
 
 class NvlStore:
@@ -109,6 +121,10 @@ class NvlStore:
         self.decoupled = world > 1 and ((mode == "sync" and self.replicas > 0) or
                                         (mode == "async" and self.async_apply == "owner"))
         self._service = None
+        # bcast=False (pull mode): the copies stay with the variable's home rank, consumers fetch them
+        # over NVLink inside their GEMMs, gated row block by row block on readiness flags; the push then
+        # does not wait for the other owners at its end
+        self.pull_flags = (not bcast) and world > 1 and mode == "sync" and not self.decoupled
         self.device = torch.device(device if device is not None else "cuda:%d" % torch.cuda.current_device())
         self.layout: Dict[str, _VarLayout] = {}
         self._opt_of: Dict[str, Optimizer] = {}
@@ -164,6 +180,12 @@ class NvlStore:
         self._pad_off = take(self.PAD_WORDS * 4)
         self._ctrl_off = take(CTRL_WORDS * 4)
         self._wctrl_off = take(CTRL_WORDS * 4)          # worker-side words of the decoupled protocol
+        # readiness words: one per (variable, row block) -- written by the block's owner on every rank,
+        # watched by consumers that pull the copies (bcast=False); and the owners' per-block counters
+        nv = sum(len(op.var_list) for op in self.model.train_ops)
+        self._ready_words = max(1, nv * max(1, self.world))
+        self._ready_off = take(self._ready_words * 4)
+        self._segdone_off = take(self._ready_words * 4)
         self._gs_off = self._ctrl_off + 4 * CTRL_GLOBAL_STEP
         # Adam beta powers: one {b1p, b2p} pair per Adam optimizer
         self._beta_off: Dict[int, int] = {}
@@ -182,6 +204,7 @@ class NvlStore:
             L.blocks = self._row_blocks(L.rows, L.cols, L.owner) if len(s.shape) == 2 else [(0, 1, L.owner)]
             L.grad_off = g
             g += round_up(s.numel, 4)
+            L.ready_base = len(self.layout) * max(1, self.world)      # first readiness word of this variable
             self.layout[s.name] = L
         self._grad_elems = g
         self._grad_off = take(g * 4)
@@ -216,6 +239,7 @@ class NvlStore:
         self._t_arena = h.ptr_table(self._arena_off)
         self._t_farena = h.ptr_table(self._farena_off)
         self._t_pad = h.ptr_table(self._pad_off)
+        self._t_ready = h.ptr_table(self._ready_off)
         # single-entry tables for the async launch (world == 1 from the kernel's viewpoint)
         self._t_grads_self = torch.tensor([h.ptr(self._grad_off)], dtype=torch.int64, device=self.device)
 
@@ -236,7 +260,7 @@ class NvlStore:
     def zero_in_before_grads(self) -> bool:
         """Async with owner-side apply: the gradient buffer may only be cleared once every owner has
         acknowledged the previous gradient, so :meth:`before_grads` does it."""
-        return self.decoupled and self.mode == "async"
+        return (self.decoupled and self.mode == "async") or (self.pull_flags and not self.owner_zeroes_grads)
 
     def _build_segs(self, owned_only: bool, peer_state: bool, kind_override: Optional[int],
                     op_names: Optional[List[str]] = None):
@@ -247,11 +271,16 @@ class NvlStore:
         if op_names is not None:
             wanted = {n for op in self.model.train_ops if op.name in op_names for n in op.var_list}
         for name, L in self.layout.items():
+            refresh_only = False
             if wanted is not None and name not in wanted:
-                continue
+                if not (self.pull_flags and kind_override is None):
+                    continue
+                # pull mode: consumers wait for EVERY variable's flag to reach the new step token, so the
+                # variables this push does not update are re-published unchanged
+                refresh_only = True
             opt = self._opt_of[name]
             hv = opt.hyper_vector()
-            for (r0, r1, owner) in L.blocks:
+            for bi, (r0, r1, owner) in enumerate(L.blocks):
                 if owned_only and owner != self.rank:
                     continue
                 two_d = len(L.spec.shape) == 2
@@ -259,7 +288,7 @@ class NvlStore:
                 numel = (r1 - r0) * L.cols if two_d else L.spec.numel
                 s = PushSeg()
                 s.grad_offset, s.numel, s.cols = L.grad_off + e0, numel, L.cols
-                s.opt_kind = opt.kind if kind_override is None else kind_override
+                s.opt_kind = -1 if refresh_only else (opt.kind if kind_override is None else kind_override)
                 s.lr, s.h1, s.h2, s.eps = hv
                 st_rank = owner if peer_state else self.rank
                 s.master = h.peer_ptr(st_rank, L.master_off + 4 * e0)
@@ -275,7 +304,8 @@ class NvlStore:
                 s.home = L.owner            # bcast=0: every row block lands in the arena of the variable's home rank
                 s.bcast = 1 if self.bcast else 0
                 s.flags = SEG_ZERO_GRAD if (name in self._zero_after_push and kind_override is None
-                                            and self.owner_zeroes_grads) else 0
+                                            and self.owner_zeroes_grads and not refresh_only) else 0
+                s.ready_slot = (L.ready_base + bi + 1) if self.pull_flags else 0
                 # rounds of work: one block iteration covers TU 32x32 tiles, or 256 threads x U groups of
                 # four (TU, U as in csrc/push.cu for this world's template bucket)
                 kw = 1 if peer_state else self.world        # legacy async launches run with world == 1
@@ -320,6 +350,7 @@ class NvlStore:
         m.rows, m.cols = L.rows, L.cols
         m.remote = rank is not None and rank != self.rank
         m.t = self.heap.tensor(self._arena_off + 2 * L.w_off, (L.rows, L.ld_w), torch.bfloat16, rank)
+        m.ready = self._ready_info(L, dim=1)
         return m
 
     def wt(self, name: str, rank: Optional[int] = None) -> BMat:
@@ -329,7 +360,35 @@ class NvlStore:
         m.rows, m.cols = L.cols, L.rows
         m.remote = rank is not None and rank != self.rank
         m.t = self.heap.tensor(self._arena_off + 2 * L.wt_off, (L.cols, L.ld_wt), torch.bfloat16, rank)
+        m.ready = self._ready_info(L, dim=0)
         return m
+
+    def _ready_info(self, L: _VarLayout, dim: int) -> Optional[ReadyInfo]:
+        """Flags of ``L``'s row blocks for a consuming GEMM: ``dim`` 0 when the blocks cut the GEMM's K
+        (the transposed copy is B), 1 when they cut its N (the natural copy is B)."""
+        if not self.pull_flags:
+            return None
+        nblk = len(L.blocks)
+        rows = L.blocks[0][1] - L.blocks[0][0]
+        first = 0
+        for i, (_, _, owner) in enumerate(L.blocks):
+            if owner == self.rank:
+                first = i
+        return ReadyInfo(self.heap.ptr(self._ready_off + 4 * L.ready_base), self.heap.ptr(self._ctrl_off + 4 * CTRL_STEP),
+                         max(1, rows), dim, nblk, first, self.heap.ptr(self._ctrl_off + 4 * CTRL_STATUS), self.timeout_ns)
+
+    def ready_for(self, name: str) -> Optional[ReadyInfo]:
+        """Readiness flag of a 1-D variable (bias): the consuming GEMM's epilogue waits for it."""
+        return self._ready_info(self.layout[name], dim=0)
+
+    def wait_all_params(self) -> None:
+        """Pull mode: block the stream until every owner has published this step's parameters -- for
+        consumers that do not watch readiness flags themselves (the LSTM kernels' weight prologue), and
+        once before the first gradient of a step is written (the owners have then also finished reading
+        the previous gradients)."""
+        if self.pull_flags:
+            _lib.check(_lib.lib().psb_wait_params_token(self.pad.data_ptr(), self.world, self.ctrl.data_ptr(),
+                                                        self.timeout_ns, _lib.current_stream_ptr()), "psb_wait_params_token")
 
     def vec(self, name: str, rank: Optional[int] = None) -> torch.Tensor:
         """fp32 compute copy of a 1-D variable."""
@@ -474,6 +533,8 @@ class NvlStore:
         d.blocks_per_seg = gx
         d.prof = self.prof.data_ptr()
         d.timeout_ns = self.timeout_ns
+        if self.pull_flags:
+            d.ready_ptrs, d.seg_done = self._t_ready.data_ptr(), self.heap.ptr(self._segdone_off)
         if sync:
             d.grad_ptrs, d.world, d.rank = self._t_grads.data_ptr(), self.world, self.rank
             d.inv_replicas = 1.0 / self.world
@@ -512,10 +573,11 @@ class NvlStore:
         async apply the gradient buffer is still owned by the ps shards until each of them has
         acknowledged the previous gradient: wait for that (normally long done: it overlapped the
         forward pass), then clear what the backward kernels accumulate into."""
-        if self.zero_in_before_grads:
+        if self.decoupled and self.mode == "async":
             self._commit(1)
-            if self._zero_after_push:
-                self.grads.zero_()
+        self.wait_all_params()
+        if self.zero_in_before_grads and self._zero_after_push:
+            self.grads.zero_()
 
     def start_service(self, poll_us: int = 0) -> None:
         """Start this rank's ps service thread (collective: call on every rank after the compute
@@ -585,6 +647,8 @@ class NvlStore:
         delta = sum(1 for op in self.model.train_ops if op.increments_global_step and
                     (op_names is None or op.name in op_names))
         d = self._desc(segs, n, gx, sync, delta, True, op_names)
+        if self.pull_flags:
+            d.phases = PH_SIGNAL_GRADS | PH_WAIT_GRADS | PH_APPLY | PH_SIGNAL_PARAMS     # no wait for the other owners
         _lib.check(_lib.lib().psb_push_apply(ctypes.byref(d), stream), "psb_push_apply")
         self._push_count += 1
 

@@ -68,17 +68,34 @@ typedef struct psb_epilogue {
     int b_static;      /* 1: B (e.g. a weight copy) was not produced by the kernel launched just before this
                           one on the stream, so its first pipeline stages may be fetched while that kernel is
                           still finishing (programmatic dependent launch); 0 when in doubt */
+    /* Parameter pull with per-block readiness.  B is a compute copy of a variable that the owners'
+     * push kernels refresh row block by row block (psb_push_seg_t.ready_idx); `ready` points at this
+     * rank's flag words for that variable, one per row block.  The TMA producer requests a tile only
+     * after the flag of the row block it belongs to has reached *ready_step, visiting the k-blocks from
+     * `ready_first` on (fixed order per rank: results stay bit-reproducible), so the tensor cores start
+     * on the blocks that have arrived while the rest is still crossing NVLink.  All NULL/0 = off. */
+    const uint32_t* ready;
+    const uint32_t* ready_step;
+    int ready_rows;    /* variable rows per block */
+    int ready_dim;     /* 0: the row blocks partition K of this GEMM (B = W^T copy); 1: they partition N (B = W copy) */
+    int ready_nblk;
+    int ready_first;
+    const uint32_t* bias_ready;   /* flag word of the bias variable, waited for by the epilogue warps */
+    uint32_t* ready_status;       /* receives PSB_PUSH_ST_TIMEOUT_PARAMS if a wait ends on ready_timeout_ns */
+    uint64_t ready_timeout_ns;
+    int pull_mode;     /* psb_gemm_bf16_pull only: 0 = TMA on the peer-mapped address, 1 = 128-bit ld.global */
 } psb_epilogue_t;
 
 int psb_gemm_bf16(const void* A, int lda, const void* B, int ldb, int M, int N, int K,
                   const psb_epilogue_t* epi, int block_n /*0 = auto*/, void* stream);
 
 /* Parameter pull fused into the consuming GEMM.  Same contract as psb_gemm_bf16, but B (the
- * weight copy, [N, ldb] bf16, pad columns zero) may live in ANOTHER GPU's memory: the producer
- * warp fetches each B tile with 128-bit loads over NVLink straight into the swizzled
- * shared-memory stage (no TMA descriptor on the peer address, no local staging copy) while
- * the tensor cores work on the previous stages; A still arrives by TMA from local memory.
- * `epi->bias` may be a peer pointer too.
+ * weight copy, [N, ldb] bf16, pad columns zero) may live in ANOTHER GPU's memory (a CUDA-IPC peer
+ * mapping): its tiles are fetched over NVLink by TMA -- a tensor map over the peer address --
+ * straight into the swizzled shared-memory stages while the tensor cores work on the previous
+ * stages, optionally gated tile by tile on the owners' readiness flags (epi->ready ...).
+ * epi->pull_mode = 1 selects the older producer-warp variant (128-bit ld.global into the swizzled
+ * stage).  A arrives by TMA from local memory; `epi->bias` may be a peer pointer too.
  * ref: the per-step ps->worker variable reads TF inserts for encoder:69-83, gan:77-90, lstm:53. */
 int psb_gemm_bf16_pull(const void* A, int lda, const void* B_peer, int ldb, int M, int N, int K,
                        const psb_epilogue_t* epi, int block_n /*0 = auto*/, void* stream);
@@ -229,6 +246,12 @@ typedef struct psb_push_seg {
                                segment once (block_x = 0) and launch grid.x = blocks_per_seg blocks per entry, or
                                list it nblocks times with block_x = 0..nblocks-1 and launch ONE block per entry:
                                segments of very different sizes then share one wave without idle blocks */
+    uint32_t ready_slot;    /* 1 + index of this segment's readiness word, 0 = none.  When the LAST block of the
+                               segment has finished, the step token is published in that word of every rank's
+                               readiness array (desc->ready_ptrs): consumers that pull the copies (psb_gemm_bf16 /
+                               _pull with epi->ready) start on this row block without waiting for the rest of
+                               the push */
+    uint32_t reserved_;
 } psb_push_seg_t;
 /* After reading them, overwrite this segment's gradients with zero in EVERY rank's gradient
  * buffer, so producers that accumulate (bias column sums, split-K partial sums) need no separate
@@ -271,6 +294,8 @@ typedef struct psb_push_desc {
                                         actually taken; gradients that arrive later are never read.  <= 0 or >= world: all */
     uint64_t timeout_ns;             /* bound on every cross-GPU wait (globaltimer); 0 = none.  On expiry the kernel
                                         applies nothing, sets local_ctrl[3] and returns */
+    uint32_t* const* ready_ptrs;     /* DEVICE array [world]: every rank's readiness array (NULL = no per-segment flags) */
+    uint32_t* seg_done;              /* DEVICE, zeroed: one finished-block counter per readiness word (local) */
 } psb_push_desc_t;
 
 #define PSB_PUSH_CTRL_WORDS 64
@@ -298,7 +323,7 @@ int psb_push_apply(const psb_push_desc_t* desc, void* stream);
  * start-up, a latency path where cudaMalloc's implicit synchronisation is unacceptable).
  * This entry point has no counterpart in the reference; it exists only for those callers.
  * The kernel's control words, the segment table and the pointer tables live in one static
- * device array inside the library image (8960 bytes = 8.75 KiB per GPU, held until process
+ * device array inside the library image (9472 bytes = 9.25 KiB per GPU, held until process
  * exit), so the tables are given as HOST arrays: host_segs[nseg], and host_grad_ptrs[world],
  * host_arena_ptrs[n_arenas], host_farena_ptrs[n_arenas], host_pad_ptrs[world] (may be NULL
  * when world == 1); they are copied with cudaMemcpyAsync on `stream`, so keep them valid and
@@ -343,6 +368,10 @@ int psb_ps_service_start(const psb_push_desc_t* desc, int poll_us, void** handle
 int psb_ps_service_stop(void* handle, uint64_t* launches /* optional out */);
 /* Block the stream until every rank has published params-ready >= step_id on `pad`. */
 int psb_wait_params(uint32_t* pad, int world, uint32_t step_id, void* stream);
+/* The same against the step token in local_ctrl[2] (what this rank's last push recorded), bounded by
+ * timeout_ns with the outcome in local_ctrl[3]: for consumers that do not watch readiness flags when
+ * the push itself no longer waits for the other owners (pull mode). */
+int psb_wait_params_token(uint32_t* pad, int world, uint32_t* local_ctrl, uint64_t timeout_ns, void* stream);
 
 /* ------------------------------------------------------------------ peer memory (CUDA IPC)
  * psb_heap_alloc cudaMalloc's and zeroes one "symmetric heap" (THE allocating call of this

@@ -82,19 +82,53 @@ def test_gemm_dact_colsum(dact):
 @pytest.mark.parametrize("M,N,K,bn", [(256, 256, 784, 0), (128, 784, 256, 64), (128, 1, 256, 0),
                                       (128, 256, 100, 32), (300, 520, 456, 128), (256, 512, 1024, 256)])
 def test_gemm_pull_variant_matches(M, N, K, bn):
-    """psb_gemm_bf16_pull (B fetched by ld.global into swizzled smem) == the TMA kernel == oracle."""
+    """psb_gemm_bf16_pull -- B by TMA over the (peer) address, or by the producer warp's ld.global into
+    swizzled smem -- == the plain TMA kernel == oracle."""
     from psb200.ops import cuda as K_
     a, b = _mats(M, N, K, 3)
     bias = torch.randn(N, device="cuda")
     A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
-    o1, o2 = K_.BMat(M, N), K_.BMat(M, N)
+    o1, o2, o3 = K_.BMat(M, N), K_.BMat(M, N), K_.BMat(M, N)
     K_.gemm(A, B, bias=bias, act=1, out=o1, block_n=bn)
     B.remote = True
     K_.gemm(A, B, bias=bias, act=1, out=o2, block_n=bn)
+    K_.gemm(A, B, bias=bias, act=1, out=o3, block_n=bn, pull_mode=1)
     torch.cuda.synchronize()
     ref = torch.sigmoid(A.float() @ B.float().t() + bias)
     assert (o2.float() - ref).abs().max().item() < 2e-2
-    assert torch.equal(o1.t, o2.t)
+    assert torch.equal(o1.t, o2.t) and torch.equal(o1.t, o3.t)
+
+
+@pytest.mark.parametrize("dim,nblk,first", [(0, 4, 2), (0, 1, 0), (1, 4, 1), (0, 8, 7)])
+def test_gemm_with_readiness_flags(dim, nblk, first):
+    """Tiles gated on per-row-block readiness flags (the pull fused into the GEMM): with every flag
+    already at the expected step the result equals the ungated GEMM up to the order in which the
+    k-blocks are accumulated (dim 0 visits them starting at `first`); a flag that never arrives ends
+    in the timeout status instead of a hang."""
+    from psb200.ops import cuda as K_
+    from psb200.store.nvl import ReadyInfo
+    M, N, K = 256, 512, 768
+    a, b = _mats(M, N, K, 5)
+    bias = torch.randn(N, device="cuda")
+    A, B = K_.BMat.from_tensor(a), K_.BMat.from_tensor(b)
+    o1, o2 = torch.zeros(M, N, device="cuda"), torch.zeros(M, N, device="cuda")
+    K_.gemm(A, B, bias=bias, out_f32=o1)
+    flags = torch.full((nblk + 1,), 7, dtype=torch.int32, device="cuda")
+    step = torch.tensor([7], dtype=torch.int32, device="cuda")
+    status = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rows = ((K if dim == 0 else N) + nblk - 1) // nblk
+    B.ready = ReadyInfo(flags.data_ptr(), step.data_ptr(), rows, dim, nblk, first, status.data_ptr(), int(2e8))
+    binfo = ReadyInfo(flags.data_ptr() + 4 * nblk, step.data_ptr(), 1, 0, 1, 0, status.data_ptr(), int(2e8))
+    K_.gemm(A, B, bias=bias, bias_ready=binfo, out_f32=o2)
+    torch.cuda.synchronize()
+    assert int(status) == 0
+    assert torch.allclose(o1, o2, rtol=1e-4, atol=1e-3 * o1.abs().max().item())
+    if dim == 1 or first == 0:
+        assert torch.equal(o1, o2)
+    flags[nblk - 1] = 6                       # one row block never becomes ready
+    K_.gemm(A, B, bias=bias, out_f32=o2)
+    torch.cuda.synchronize()
+    assert int(status) == 2                   # PSB_PUSH_ST_TIMEOUT_PARAMS, after ~0.2 s
 
 
 @pytest.mark.parametrize("split,stride", [(2, 0), (4, 0), (2, 1), (4, 1)])
