@@ -23,7 +23,7 @@ W = {
 }
 idx = {k: hdr.index(k) for k in W if k in hdr}
 stall = [(i, h) for i, h in enumerate(hdr) if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")]
-lines = ["# " + title, "", "Source: `%s` (`ncu --set full --clock-control none --import-source on`, one B200)." % rep.split("/")[-1],
+lines = ["# " + title, "", "Source: `%s` (`ncu --set full --clock-control none`, one B200)." % rep.split("/")[-1],
          "Durations under ncu are serialised/cold-cache: compare shares, not absolutes.", "",
          "| " + " | ".join(W[k] for k in idx) + " | top stalls (warp-cycles per issue) |", "|" + "---|" * (len(idx) + 1)]
 for r in rows[2:]:
