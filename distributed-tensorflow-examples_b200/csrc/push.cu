@@ -81,6 +81,7 @@ struct PushArgs {
     int async_sgd_atomic;              // 1: SGD segments use atomicAdd on master (peer atomics)
     int phases;                        // PSB_PUSH_* bits
     int replicas;                      // gradients to aggregate (R of N); <= 0 or >= world: all
+    int big_tiles;                     // the launch carries the dynamic shared memory of the 128x128-tile path
     unsigned long long* prof;          // optional [8]: t0, t1, -, -, sum(wait grads), sum(apply), sum(wait params), calls
     unsigned long long timeout_ns;     // 0 = wait forever
     uint32_t* const* ready_ptrs;       // [world] readiness arrays (per-segment "this row block is refreshed" flags)
@@ -218,7 +219,7 @@ __device__ __forceinline__ void apply4(const OptCtx& o, const float4 (&t)[MAXW],
 }
 
 // Templated on the largest world the register-resident batch of peer loads is sized for.
-template <int MAXW>
+template <int MAXW, bool kBig>
 __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a) {
     __shared__ const float* s_grad[kMaxWorld];
     __shared__ __nv_bfloat16* s_arena[kMaxWorld];
@@ -228,6 +229,10 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
     __shared__ bool is_last;
     __shared__ bool seg_last;
     __shared__ __nv_bfloat16 tile[2][32][34];
+    // 128x128 tile of new weights (+8 pad: 272-byte rows): dynamic, only launches that have
+    // PSB_SEG_BIG_TILES segments ask for it (34816 bytes)
+    extern __shared__ __align__(16) uint8_t big_raw[];
+    __nv_bfloat16 (*big)[136] = reinterpret_cast<__nv_bfloat16 (*)[136]>(big_raw);      // kBig instantiation only
 
     const int tid = threadIdx.x;
     const bool first_block = blockIdx.x == 0 && blockIdx.y == 0;
@@ -353,7 +358,100 @@ __global__ void __launch_bounds__(kPushThreads, 2) push_apply_kernel(PushArgs a)
         const bool need_g = o.kind >= 0;
         const bool zero_g = (s.flags & PSB_SEG_ZERO_GRAD) != 0 && need_g;
         const int n_dst = s.bcast ? a.n_arenas : 1;
-        if (s.w_off >= 0 || s.wt_off >= 0) {
+        if (kBig && (s.w_off >= 0 || s.wt_off >= 0) && (s.flags & PSB_SEG_BIG_TILES) && !atomic_sgd) {
+            // ---- big matrices: 128x128 tiles.  The reduction and the optimizer step run over the tile in
+            // sixteen 32x32 pieces (MAXW peer loads in flight per thread each), the new weights are
+            // collected as bf16 in shared memory, and BOTH copies then leave in 16-byte stores that form
+            // 256-byte runs per row (natural copy) and per column (transposed copy).  Over NVLink that is
+            // what matters: the 64-byte runs of the small-tile path reach about a tenth of the link rate.
+            const int rows = static_cast<int>(s.numel / s.cols);
+            const int tc = (cols + 127) >> 7, trw = (rows + 127) >> 7;
+            const int ntiles = tc * trw;
+            const int ty = tid >> 3, tx4 = (tid & 7) * 4;
+            const bool v4 = aligned && (cols % 4 == 0);
+            for (int T = bx; T < ntiles; T += nb) {
+                const int R0 = (T / tc) * 128, C0 = (T % tc) * 128;
+#pragma unroll 1
+                for (int sub = 0; sub < 16; ++sub) {
+                    const int lr = (sub >> 2) * 32 + ty, lc = (sub & 3) * 32 + tx4;
+                    const int r = R0 + lr, c = C0 + lc;
+                    const bool live = r < rows && c < cols;
+                    const int nv = live ? min(4, cols - c) : 0;
+                    float4 t[MAXW];
+                    float4 w = make_float4(0.f, 0.f, 0.f, 0.f), v0 = w, v1 = w;
+                    if (live) {
+                        const size_t i = static_cast<size_t>(r) * cols + c;
+                        if (need_g) {
+#pragma unroll
+                            for (int rk = 0; rk < MAXW; ++rk)
+                                if (rk < a.world && ((mask >> rk) & 1u)) t[rk] = ld4_cg(s_grad[rk] + s.grad_offset + i, v4, nv);
+                        }
+                        w = ld4(master + i, v4, nv);
+                        if (o.kind > 0) { v0 = ld4(s0 + i, v4, nv); v1 = ld4(s1 + i, v4, nv); }
+                        if (need_g) apply4<MAXW>(o, t, a.world, mask, each, inv, w, v0, v1);
+                        st4(master + i, w, v4, nv);
+                        if (o.kind > 0) { st4(s0 + i, v0, v4, nv); st4(s1 + i, v1, v4, nv); }
+                        if (zero_g) {
+                            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+                            for (int rk = 0; rk < a.world; ++rk)
+                                st4(const_cast<float*>(s_grad[rk]) + s.grad_offset + i, z, v4, nv);
+                        }
+                    }
+                    const float wv[4] = {w.x, w.y, w.z, w.w};
+                    uint2 pk;
+                    pk.x = pack_bf16(nv > 0 ? wv[0] : 0.f, nv > 1 ? wv[1] : 0.f);
+                    pk.y = pack_bf16(nv > 2 ? wv[2] : 0.f, nv > 3 ? wv[3] : 0.f);
+                    *reinterpret_cast<uint2*>(&big[lr][lc]) = pk;
+                }
+                __syncthreads();
+                // natural copy: 128 rows x 16 chunks of 8 columns (16 bytes)
+                if (s.w_off >= 0) {
+                    for (int idx = tid; idx < 128 * 16; idx += kPushThreads) {
+                        const int lr = idx >> 4, lc = (idx & 15) * 8;
+                        const int r = R0 + lr, c = C0 + lc;
+                        if (r >= rows || c >= cols) continue;
+                        const uint4 v = *reinterpret_cast<const uint4*>(&big[lr][lc]);
+                        const size_t off = static_cast<size_t>(s.w_off) + static_cast<size_t>(r) * s.ld_w + c;
+                        const bool full = (c + 8 <= cols) && ((off & 7) == 0);
+                        for (int d = 0; d < n_dst; ++d) {
+                            __nv_bfloat16* pd = s_arena[s.bcast ? d : s.home] + off;
+                            if (full) {
+                                *reinterpret_cast<uint4*>(pd) = v;
+                            } else {
+                                for (int e = 0; e < 8 && c + e < cols; ++e) pd[e] = big[lr][lc + e];
+                            }
+                        }
+                    }
+                }
+                // transposed copy: 128 columns x 16 chunks of 8 rows (16 bytes of one wt row)
+                if (s.wt_off >= 0) {
+                    for (int idx = tid; idx < 128 * 16; idx += kPushThreads) {
+                        const int lc = idx >> 4, lr0 = (idx & 15) * 8;
+                        const int cg = C0 + lc, rg = R0 + lr0;
+                        if (cg >= cols || rg >= rows) continue;
+                        __nv_bfloat16 col[8];
+#pragma unroll
+                        for (int k = 0; k < 8; ++k) col[k] = big[lr0 + k][lc];
+                        const size_t off = static_cast<size_t>(s.wt_off) + static_cast<size_t>(cg) * s.ld_wt + rg;
+                        const bool full = (rg + 8 <= rows) && ((off & 7) == 0);
+                        uint4 v;
+                        v.x = static_cast<uint32_t>(__bfloat16_as_ushort(col[0])) | (static_cast<uint32_t>(__bfloat16_as_ushort(col[1])) << 16);
+                        v.y = static_cast<uint32_t>(__bfloat16_as_ushort(col[2])) | (static_cast<uint32_t>(__bfloat16_as_ushort(col[3])) << 16);
+                        v.z = static_cast<uint32_t>(__bfloat16_as_ushort(col[4])) | (static_cast<uint32_t>(__bfloat16_as_ushort(col[5])) << 16);
+                        v.w = static_cast<uint32_t>(__bfloat16_as_ushort(col[6])) | (static_cast<uint32_t>(__bfloat16_as_ushort(col[7])) << 16);
+                        for (int d = 0; d < n_dst; ++d) {
+                            __nv_bfloat16* pd = s_arena[s.bcast ? d : s.home] + off;
+                            if (full) {
+                                *reinterpret_cast<uint4*>(pd) = v;
+                            } else {
+                                for (int k = 0; k < 8 && rg + k < rows; ++k) pd[k] = col[k];
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        } else if (s.w_off >= 0 || s.wt_off >= 0) {
             // ---- matrices: 32x32 tiles so that BOTH bf16 copies are written in full 32-byte
             // sectors (the transposed copy goes through a shared-memory transpose).  Two tiles
             // per iteration: every peer load of both tiles first, then the math, then the stores.
@@ -715,17 +813,18 @@ static void fill_args(PushArgs& a, const psb_push_desc_t* d) {
         }
     }
     a.replicas = d->replicas;
+    a.big_tiles = d->big_tiles;
     a.prof = reinterpret_cast<unsigned long long*>(d->prof);
     a.timeout_ns = d->timeout_ns;
     a.ready_ptrs = d->seg_done != nullptr ? d->ready_ptrs : nullptr;
     a.seg_done = d->seg_done;
 }
 
-static int launch_push(const PushArgs& a, dim3 grid, cudaStream_t st, bool pdl) {
+static int launch_push(const PushArgs& a, dim3 grid, cudaStream_t st, bool pdl, bool big_tiles = false) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kPushThreads);
-    cfg.dynamicSmemBytes = 0;
+    cfg.dynamicSmemBytes = big_tiles ? 128 * 136 * 2 : 0;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
@@ -733,11 +832,19 @@ static int launch_push(const PushArgs& a, dim3 grid, cudaStream_t st, bool pdl) 
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
     cudaError_t e;
-    if (a.world <= 1) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<1>, a);
-    else if (a.world <= 2) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<2>, a);
-    else if (a.world <= 4) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<4>, a);
-    else if (a.world <= 8) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<8>, a);
-    else e = cudaLaunchKernelEx(&cfg, push_apply_kernel<16>, a);
+    // the 128x128-tile path is a separate instantiation: launches without big segments run exactly
+    // the small-tile code (registers, shared memory) they always ran
+    if (big_tiles) {
+        if (a.world <= 1) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<1, true>, a);
+        else if (a.world <= 2) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<2, true>, a);
+        else if (a.world <= 4) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<4, true>, a);
+        else if (a.world <= 8) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<8, true>, a);
+        else e = cudaLaunchKernelEx(&cfg, push_apply_kernel<16, true>, a);
+    } else if (a.world <= 1) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<1, false>, a);
+    else if (a.world <= 2) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<2, false>, a);
+    else if (a.world <= 4) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<4, false>, a);
+    else if (a.world <= 8) e = cudaLaunchKernelEx(&cfg, push_apply_kernel<8, false>, a);
+    else e = cudaLaunchKernelEx(&cfg, push_apply_kernel<16, false>, a);
     if (e != cudaSuccess) return fail(PSB_ERR_CUDA, "push_apply launch failed: %s", cudaGetErrorString(e));
     return PSB_OK;
 }
@@ -759,7 +866,7 @@ extern "C" int psb_push_apply(const psb_push_desc_t* d, void* stream) {
     // No co-residency requirement: a block only ever waits for peers' block (0,0) -- which is in the
     // first wave of its grid and waits for nobody in its own grid -- and the last block to finish for
     // the owners' final flags.
-    rc = launch_push(a, grid, static_cast<cudaStream_t>(stream), true);
+    rc = launch_push(a, grid, static_cast<cudaStream_t>(stream), true, d->big_tiles != 0);
     if (rc != PSB_OK) return rc;
     return after_launch("push_apply");
 }
@@ -906,7 +1013,7 @@ extern "C" int psb_push_apply_noalloc(const psb_push_seg_t* host_segs, int nseg,
     fill_args(a, d);
     a.n_arenas = n_arenas;
     // the launch follows copies, not a kernel: no programmatic dependent launch here
-    rc = launch_push(a, grid, st, false);
+    rc = launch_push(a, grid, st, false, d->big_tiles != 0);
     if (rc != PSB_OK) return rc;
     return after_launch("push_apply_noalloc");
 }

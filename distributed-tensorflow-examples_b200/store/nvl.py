@@ -53,10 +53,11 @@ class PushDesc(Structure):
                 ("global_step", c_void_p), ("step_delta", c_int), ("async_sgd_atomic", c_int),
                 ("signal_params", c_int), ("blocks_per_seg", c_int), ("prof", c_void_p),
                 ("phases", c_int), ("replicas", c_int), ("timeout_ns", c_uint64),
-                ("ready_ptrs", c_void_p), ("seg_done", c_void_p)]
+                ("ready_ptrs", c_void_p), ("seg_done", c_void_p), ("big_tiles", c_int)]
 
 
 SEG_ZERO_GRAD = 1
+SEG_BIG_TILES = 2
 CTRL_WORDS = 64                      # PSB_PUSH_CTRL_WORDS
 CTRL_STEP, CTRL_STATUS, CTRL_ABORT, CTRL_APPLIED = 2, 3, 4, 7
 CTRL_GLOBAL_STEP = 48                # global_step lives in a spare word of the control block: one D2H reads both
@@ -97,6 +98,8 @@ class NvlStore:
 
     PAD_WORDS = 64
     PARTITION_MIN_ELEMS = 8192
+    # row blocks at least this big are pushed in 128x128 tiles (256-byte runs); PSB200_BIG_TILES_MIN overrides (tests)
+    BIG_TILES_MIN_ELEMS = int(__import__("os").environ.get("PSB200_BIG_TILES_MIN", 1 << 20))
 
     def __init__(self, model: Model, registry: VariableRegistry, rank: int = 0, world: int = 1,
                  group=None, mode: str = "sync", bcast: bool = True, device=None, partition: bool = True,
@@ -310,7 +313,10 @@ class NvlStore:
                 # four (TU, U as in csrc/push.cu for this world's template bucket)
                 kw = 1 if peer_state else self.world        # legacy async launches run with world == 1
                 maxw = 1 << max(0, (kw - 1).bit_length())
-                if two_d:
+                if two_d and numel >= self.BIG_TILES_MIN_ELEMS and (r1 - r0) >= 128 and L.cols >= 128 and not peer_state:
+                    s.flags |= SEG_BIG_TILES
+                    rounds.append((((r1 - r0) + 127) // 128) * ((L.cols + 127) // 128))
+                elif two_d:
                     units = (((r1 - r0) + 31) // 32) * ((L.cols + 31) // 32)
                     tu = 1 if maxw >= 8 else 2
                     rounds.append(max(1, (units + tu - 1) // tu))
@@ -336,6 +342,7 @@ class NvlStore:
         arr = (PushSeg * max(len(items), 1))(*items)
         raw = bytes(arr) if items else b"\0" * ctypes.sizeof(PushSeg)
         dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
+        dev._psb_big_tiles = any(it.flags & SEG_BIG_TILES for it in items)
         return dev, len(items), 1
 
     def _beta_owner(self, op_index: int) -> int:
@@ -525,6 +532,7 @@ class NvlStore:
               op_names: Optional[List[str]] = None) -> PushDesc:
         d = PushDesc()
         d.segs, d.nseg = segs.data_ptr(), nseg
+        d.big_tiles = 1 if getattr(segs, "_psb_big_tiles", False) else 0
         d.arena_ptrs, d.farena_ptrs = self._t_arena.data_ptr(), self._t_farena.data_ptr()
         d.pad_ptrs = self._t_pad.data_ptr()
         d.n_arenas = self.world

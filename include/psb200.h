@@ -257,6 +257,10 @@ typedef struct psb_push_seg {
  * buffer, so producers that accumulate (bias column sums, split-K partial sums) need no separate
  * clear before the next step. */
 #define PSB_SEG_ZERO_GRAD 1u
+/* Matrix segment processed in 128x128 tiles whose bf16 copies leave in 16-byte stores forming
+ * 256-byte runs (what large copies written into peers' arenas over NVLink need); for matrices of
+ * at least 128 x 128.  Without it: 32x32 tiles, one wave of blocks for small variables. */
+#define PSB_SEG_BIG_TILES 2u
 
 typedef struct psb_beta_update {
     float* beta_pow;        /* {beta1_power, beta2_power} */
@@ -296,6 +300,8 @@ typedef struct psb_push_desc {
                                         applies nothing, sets local_ctrl[3] and returns */
     uint32_t* const* ready_ptrs;     /* DEVICE array [world]: every rank's readiness array (NULL = no per-segment flags) */
     uint32_t* seg_done;              /* DEVICE, zeroed: one finished-block counter per readiness word (local) */
+    int big_tiles;                   /* 1: some segment has PSB_SEG_BIG_TILES (the launch then carries 34 KiB of dynamic
+                                        shared memory; without it those segments take the small-tile path) */
 } psb_push_desc_t;
 
 #define PSB_PUSH_CTRL_WORDS 64

@@ -31,6 +31,13 @@ def test_sync_push_matches_oracle_and_is_deterministic(model):
     _run(2, "--model", model, "--mode", "sync")
 
 
+def test_sync_push_big_tile_path_across_ranks(monkeypatch):
+    """The 128x128-tile path of the push kernel (16-byte stores into every rank's arena), forced at the
+    encoder's sizes: same oracle, identical-arena and determinism checks as the small-tile path."""
+    monkeypatch.setenv("PSB200_BIG_TILES_MIN", "1024")
+    _run(2, "--model", "encoder", "--mode", "sync")
+
+
 @pytest.mark.parametrize("model", ["lstm", "gan"])
 def test_async_push_counts_every_update(model):
     _run(2, "--model", model, "--mode", "async")

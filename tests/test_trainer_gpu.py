@@ -33,10 +33,14 @@ def _apply(model, values, grads_by_op):
     return new
 
 
-@pytest.mark.parametrize("name", ["lstm", "lstm_unfused_head", "encoder", "gan"])
+@pytest.mark.parametrize("name", ["lstm", "lstm_unfused_head", "encoder", "gan", "encoder_big_tiles", "gan_big_tiles"])
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_one_step_matches_oracle(name, use_graph):
+def test_one_step_matches_oracle(name, use_graph, monkeypatch):
     from psb200.parallel.trainer import DeviceTrainer
+    from psb200.store.nvl import NvlStore
+    if name.endswith("_big_tiles"):      # the 128x128-tile path of the push kernel, forced at reference sizes
+        name = name[:-len("_big_tiles")]
+        monkeypatch.setattr(NvlStore, "BIG_TILES_MIN_ELEMS", 1024)
     kw = {"device_noise": False} if name == "gan" else {}
     if name == "lstm_unfused_head":      # head as separate kernels (the evaluation path's kernels)
         name, kw = "lstm", {"fuse_head": False}
