@@ -93,6 +93,35 @@ class _VarLayout:
                  "wt_off", "ld_wt", "f_off", "owner", "blocks", "ready_base")
 
 
+def row_blocks(rows: int, cols: int, home: int, world: int, partition: bool = True, min_elems: int = 8192):
+    """Row blocks ``(r0, r1, owner)`` of one variable.  A variable stays whole on its home rank
+    (``replica_device_setter``'s round-robin, ``encoder:111-113``) unless it is big enough for the
+    reduction to matter; then it is cut into ``world`` runs of rows (multiples of four, so both bf16
+    copies keep their 8-byte stores) owned by ranks ``home, home+1, ...`` -- a partitioned variable in
+    TF terms, same checkpoint name and shape."""
+    if not partition or world <= 1 or rows * cols < min_elems or rows < 4 * world:
+        return [(0, rows, home)]
+    per = (rows + world - 1) // world
+    per = (per + 3) // 4 * 4
+    out, r0, b = [], 0, 0
+    while r0 < rows:
+        r1 = min(rows, r0 + per)
+        out.append((r0, r1, (home + b) % world))
+        r0, b = r1, b + 1
+    return out
+
+
+def share_blocks(rounds: List[int], budget: int = 296) -> List[int]:
+    """Blocks per segment for one push launch.  ``rounds[j]`` = loop iterations segment j needs if one
+    block did it alone; the result uses the smallest number of iterations per block such that the whole
+    launch is at most ``budget`` blocks (one wave of two blocks per SM): small models then finish in a
+    single iteration per block, and no block is idle whatever the mix of segment sizes."""
+    R = 1
+    while sum((r + R - 1) // R for r in rounds) > budget:
+        R += 1
+    return [max(1, (r + R - 1) // R) for r in rounds]
+
+
 class NvlStore:
     """Parameter shards + gradient buffers of one rank, and the push launcher."""
 
@@ -154,22 +183,7 @@ class NvlStore:
 
     # ------------------------------------------------------------------ layout
     def _row_blocks(self, rows: int, cols: int, home: int):
-        """Row blocks of one variable and their owners.  A variable stays whole on its home rank
-        (``replica_device_setter``'s round-robin, ``encoder:111-113``) unless it is big enough for the
-        reduction to matter; then it is cut into ``world`` runs of rows (multiples of four, so both
-        bf16 copies keep their 8-byte stores) owned by ranks ``home, home+1, ...`` -- a partitioned
-        variable in TF terms, same checkpoint name and shape."""
-        W = self.world
-        if not self.partition or rows * cols < self.PARTITION_MIN_ELEMS or rows < 4 * W:
-            return [(0, rows, home)]
-        per = (rows + W - 1) // W
-        per = (per + 3) // 4 * 4
-        out, r0, b = [], 0, 0
-        while r0 < rows:
-            r1 = min(rows, r0 + per)
-            out.append((r0, r1, (home + b) % W))
-            r0, b = r1, b + 1
-        return out
+        return row_blocks(rows, cols, home, self.world, self.partition, self.PARTITION_MIN_ELEMS)
 
     def _plan_heap(self) -> None:
         cur = 0
@@ -328,13 +342,8 @@ class NvlStore:
         # that the whole launch fits in one wave of 2 blocks per SM: small models then finish in a single
         # iteration per block.  The table lists every segment once per block that works on it, and the
         # launch is one block per entry: no idle blocks, whatever the mix of segment sizes.
-        budget = 296
-        R = 1
-        while sum((r + R - 1) // R for r in rounds) > budget:
-            R += 1
         items = []
-        for s, r in zip(segs, rounds):
-            nb = max(1, (r + R - 1) // R)
+        for s, nb in zip(segs, share_blocks(rounds)):
             for x in range(nb):
                 it = PushSeg.from_buffer_copy(bytes(s))
                 it.nblocks, it.block_x = nb, x

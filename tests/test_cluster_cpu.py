@@ -92,6 +92,17 @@ def test_sync_mode_one_step_per_aggregate(tmp_path):
     assert n >= 10 and a[:n] == b[:n] == list(range(1, n + 1))
 
 
+def test_sync_mode_with_a_backup_worker_shuts_down_cleanly(tmp_path):
+    """--replicas_to_aggregate=1 with two workers: aggregates of one gradient, the other worker's is
+    dropped when it is stale.  When the chief reaches num_steps the worker still blocked on a token
+    must be released (sentinel token), send its done token, and the ps must quit."""
+    ps_out, w_out, _ = _run_cluster("lstm", tmp_path, ["--num_steps=15", "--sync", "--replicas_to_aggregate=1",
+                                                       "--save_model_secs=0"])
+    assert "ps 0: quitting" in ps_out[0] and "ps 0 received done 1" in ps_out[0]
+    steps = _global_steps(w_out[0]) + _global_steps(w_out[1])
+    assert max(steps) >= 15 and "Total Time" in w_out[0] and "Total Time" in w_out[1]
+
+
 def test_two_ps_placement_and_resume(tmp_path):
     # first run writes checkpoints; second run (chief restarts) must resume from the latest one
     _, w1, model_dir = _run_cluster("lstm", tmp_path, ["--num_steps=20", "--save_model_secs=1"], n_ps=2)
