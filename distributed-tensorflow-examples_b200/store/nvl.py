@@ -4,16 +4,26 @@ Replaces, on one 8xB200 box, the ps processes of the reference and the gRPC traf
 them (``replica_device_setter`` placement ``encoder:111-113``; per-step variable reads and
 ``Apply*`` updates ``encoder:137,165``, ``gan:158-159,193``, ``lstm:97,128``):
 
-* variable ``i`` (creation order) is owned by rank ``i mod world`` — fp32 master weights,
-  optimizer slots, ``global_step`` and Adam's beta powers live in the owner's HBM;
+* variable ``i`` (creation order) has its home on rank ``i mod world``; small variables live there
+  whole, big ones are cut into ``world`` runs of rows owned by ranks ``home, home+1, ...``
+  (:func:`row_blocks`) -- fp32 master weights, optimizer slots, ``global_step`` and Adam's beta
+  powers live in the owner's HBM, checkpoint names and shapes are those of the whole variable;
 * every rank keeps its gradients in one flat fp32 buffer inside a CUDA-IPC symmetric heap;
-* **push** = one ``psb_push_apply`` kernel per step: the owner P2P-loads all ranks'
-  gradient slices, averages, applies SGD/RMSProp/Adam and stores the new bf16/fp32 compute
-  copies (``sync``), or a worker applies its own gradient straight onto the owner's master
-  copy through peer pointers / peer atomics (``async``);
-* **pull** = the compute copies are either written into every rank's arena by the push
-  kernel itself (push-mode all-gather, ``bcast=True``) or read from the owner's arena by
-  the consuming kernel (``bcast=False``, e.g. the LSTM kernel's weight prologue).
+* **push** = one ``psb_push_apply`` kernel per step: every owner P2P-loads all ranks' slices of its
+  segments, averages, applies SGD/RMSProp/Adam and stores the new bf16/fp32 compute copies
+  (``sync``), or a worker applies its own gradient straight onto the owner's master copy through
+  peer pointers / peer atomics (``async``, ``async_apply="worker"``);
+* the ps role can be **decoupled** from the worker role (``replicas`` < world in sync mode,
+  ``async_apply="owner"``): a native service thread per rank (``csrc/ps_service.cu``) keeps launching
+  the push kernel in its non-blocking form -- first-R aggregation with stale gradients dropped, or
+  one optimizer step per arrived gradient -- and the workers' step only signals and waits
+  (``psb_push_commit``);
+* **pull** = the compute copies are either written into every rank's arena by the push kernel itself
+  (push-mode all-gather, ``bcast=True``) or stay in the home rank's arena and are fetched by the
+  consuming GEMMs with TMA over NVLink, tile by tile as the owners publish per-row-block readiness
+  flags (``bcast=False``);
+* every cross-GPU wait is bounded (``timeout_s``) and can be aborted from the host
+  (:meth:`NvlStore.abort`); a step that gave up raises :class:`PeerTimeoutError`.
 """
 from __future__ import annotations
 
