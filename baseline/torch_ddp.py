@@ -287,7 +287,7 @@ def run_graph(args, rank, world, local, bench, keep_group: bool = False):
                        "ms_per_step": round(ms_e2e / args.steps, 4),
                        "h2d_bytes_per_step": sum(v.numel() * 4 for v in batches[0].values()),
                        "d2h_bytes_per_step": 4},
-               "gpu_launches": 0, "final_loss": float(static_loss)}
+               "gpu_launches": 0, "final_loss": float(static_loss.detach())}
     if world > 1 and not keep_group:
         import torch.distributed as dist
         dist.barrier()

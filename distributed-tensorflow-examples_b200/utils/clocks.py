@@ -1,7 +1,7 @@
 """GPU clock / throttle sampling (the profiling recipe's ``nvidia-smi`` clocks line).
 
 A benchmark number is only trusted together with the SM clock and the throttle reasons seen
-while it was measured; :class:`ClockSampler` polls ``nvidia-smi`` every 200 ms in the
+while it was measured; :class:`ClockSampler` polls ``nvidia-smi`` every 50 ms in the
 background and summarises median SM clock, max SM clock and any active slowdown reason.
 """
 from __future__ import annotations
@@ -25,7 +25,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.idx), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
-                 "-lms", "200"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "50"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
