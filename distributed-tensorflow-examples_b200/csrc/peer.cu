@@ -93,3 +93,14 @@ extern "C" int psb_uniform_noise(float* out, int rows, int cols, int ld, float l
         static_cast<__nv_bfloat16*>(out_t), ld_t);
     return after_launch("uniform_noise");
 }
+
+// Clear a (possibly strided) 2-D region with a memset node: `rows` runs of `row_bytes` bytes, `pitch`
+// bytes apart.  What the plans use instead of a fill kernel for state that must start at zero.
+extern "C" int psb_memset_zero(void* p, size_t pitch, size_t row_bytes, size_t rows, void* stream) {
+    using namespace psb;
+    if (!p || row_bytes == 0 || rows == 0 || pitch < row_bytes) return fail(PSB_ERR_ARG, "psb_memset_zero: bad argument");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (rows == 1 || pitch == row_bytes) PSB_CUDA_OK(cudaMemsetAsync(p, 0, row_bytes * rows, st));
+    else PSB_CUDA_OK(cudaMemset2DAsync(p, pitch, 0, row_bytes, rows, st));
+    return PSB_OK;
+}

@@ -354,7 +354,7 @@ class ScaledLstmPlan(DevicePlan):
             wx_t, wh_t = wt.cols_view(0, I), wt.cols_view(I, I + H)
             bias = s.vec_src(n("bias%d" % l))
             K.gemm(inp, wx_t, out_f32=self.gx, b_static=True)                # all timesteps at once
-            self.c.zero_()
+            K.zero_(self.c)
             for t in range(T):
                 hprev = self.h0 if t == 0 else self._rows(self.Hall[l], t - 1)
                 if self.fuse_fwd:
@@ -390,7 +390,7 @@ class ScaledLstmPlan(DevicePlan):
             w = s.w_src(n("kernel%d" % l))                    # [I+H, 4H]
             wx, wh = w.rows_view(0, I), w.rows_view(I, I + H)
             gk = s.grad(n("kernel%d" % l))
-            self.dc.zero_()
+            K.zero_(self.dc)
             top = l == mdl.L - 1
             for t in range(T - 1, -1, -1):
                 dy = None
@@ -408,7 +408,7 @@ class ScaledLstmPlan(DevicePlan):
             # weight gradients of this layer in two large GEMMs over all (t, b)
             K.transpose_bf16(self.dG, self.dGT)
             # [h_{t-1}]^T: column block t holds h_{t-1}; block 0 is the zero state
-            self.HprevT.t[:, :B].zero_()
+            K.zero_(self.HprevT.t[:, :B])
             if T > 1:
                 K.transpose_bf16(self.Hall[l].rows_view(0, (T - 1) * B), self.HprevT.cols_view(B, TB))
             K.gemm(self.HprevT, self.dGT, out_f32=gk[I:])

@@ -376,3 +376,19 @@ def lstm_step_fwd(h_prev: BMat, wh_t: BMat, gx: torch.Tensor, bias: torch.Tensor
     check(_lib.lib().psb_lstm_step_fwd(h_prev.ptr, h_prev.ld, wh_t.ptr, wh_t.ld, B, H, gx.data_ptr(), gx.stride(0),
                                        bias.data_ptr(), float(forget_bias), c.data_ptr(), h_out.ptr, h_out.ld,
                                        _ptr(gates_save), _ptr(c_save), current_stream_ptr()), "psb_lstm_step_fwd")
+
+
+_lib.register_signature("psb_memset_zero", [c_void_p, ctypes.c_size_t, ctypes.c_size_t, ctypes.c_size_t, c_void_p])
+
+
+def zero_(t: torch.Tensor) -> None:
+    """Clear a contiguous tensor or a 2-D view with contiguous rows on the current stream with a memset
+    node (no kernel launch)."""
+    es = t.element_size()
+    if t.is_contiguous():
+        check(_lib.lib().psb_memset_zero(t.data_ptr(), t.numel() * es, t.numel() * es, 1, current_stream_ptr()), "psb_memset_zero")
+        return
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise ValueError("zero_: need a contiguous tensor or a 2-D view with contiguous rows")
+    check(_lib.lib().psb_memset_zero(t.data_ptr(), t.stride(0) * es, t.shape[1] * es, t.shape[0], current_stream_ptr()),
+          "psb_memset_zero")

@@ -390,6 +390,10 @@ int psb_ipc_export(void* p, unsigned char* handle64);
 int psb_ipc_open(const unsigned char* handle64, void** out);
 int psb_ipc_close(void* p);
 
+/* Zero `rows` runs of `row_bytes` bytes that lie `pitch` bytes apart (cudaMemset[2D]Async: a memset
+ * node, not a kernel) -- recurrent state that must start at zero (c_0, dc_T, h_{-1}). */
+int psb_memset_zero(void* p, size_t pitch, size_t row_bytes, size_t rows, void* stream);
+
 /* U(lo,hi) noise [rows, cols] generated on the device from (seed, *step_counter, index); the
  * kernel advances *step_counter by one, so a captured graph draws fresh noise on every replay.
  * Any of the fp32 / bf16 / bf16-transposed outputs may be NULL.  ref: np.random.uniform at gan:189. */
